@@ -1,0 +1,26 @@
+"""Initial conditions on the host: mirror of sim_make_initial_conditions (reference main.cpp:93-136)."""
+import numpy as np
+
+
+def make_initial_conditions(cfg, dtype=np.float64, rows=None):
+    """Returns (F, U) arrays of shape (ny, nx). `rows=(y_begin, y_end)` builds only a slab of global rows."""
+    p = cfg.params
+    nx, ny, L0 = p.nx, p.ny, p.L0
+    y0, y1 = (0, ny) if rows is None else rows
+    xs = (np.arange(nx, dtype=np.float64) + 0.5) / nx * L0
+    ys = (np.arange(y0, y1, dtype=np.float64) + 0.5) / ny * L0
+    X, Y = np.meshgrid(xs, ys)
+    lo = cfg.init_circle_radius - p.xi * cfg.init_circle_fade / 2
+    hi = cfg.init_circle_radius + p.xi * cfg.init_circle_fade / 2
+    r = np.hypot(cfg.init_circle_center[0] - X, cfg.init_circle_center[1] - Y)
+    within = ((cfg.init_square_from[0] <= X) & (X < cfg.init_square_to[0]) &
+              (cfg.init_square_from[1] <= Y) & (Y < cfg.init_square_to[1]))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        circle = 1 - (r - lo) / (hi - lo)             # fade 0 -> +-inf (or nan exactly on the rim), as in the reference
+    circle = np.where(circle > 1, 1.0, circle)
+    circle = np.where(circle < 0, 0.0, circle)
+    cube = np.where(within, 1.0, 0.0)
+    factor = np.where(cube > circle, cube, circle)
+    F = factor * cfg.init_inside_phi + (1 - factor) * cfg.init_outside_phi
+    U = factor * cfg.init_inside_T + (1 - factor) * cfg.init_outside_T
+    return F.astype(dtype), U.astype(dtype)

@@ -1,0 +1,213 @@
+/*
+ * pf_solver.h - C-ABI of the B200-native phase-field (Phi, "F") + temperature (T, "U") solver.
+ *
+ * This is the drop-in boundary for ONE hot path of Boostibot/bachelors: the finite-volume
+ * update behind the reference's `simulation.h` (reference simulation.h:132-145). Every entry
+ * point below names the reference interface it replaces (file:line, relative to the
+ * reference root). The reference host (main.cpp) keeps calling sim_realloc / sim_step /
+ * sim_modify*; `bachelors_b200/host/simulation_shim.cpp` implements those on top of this ABI.
+ *
+ * Plain C: opaque handle, raw device/host pointers, sizes. No torch types, no C++ types.
+ * All functions return PF_OK (0) or a negative pf_status; pf_last_error() gives the text.
+ * The library never logs and never aborts (the reference aborts on any CUDA error,
+ * cuda_util.cuh:23-41; here the error is returned to the caller).
+ *
+ * There is NO CPU fallback: without a CUDA device every call that touches the device fails
+ * with PF_ERR_NO_DEVICE.
+ */
+#ifndef PF_SOLVER_H
+#define PF_SOLVER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#  define PF_API __declspec(dllexport)
+#else
+#  define PF_API __attribute__((visibility("default")))
+#endif
+
+#define PF_ABI_VERSION 1
+
+typedef enum pf_status {
+    PF_OK               =  0,
+    PF_ERR_INVALID      = -1,  /* bad argument / size mismatch (reference: LOG_ERROR + return 0, simulation.cu:1094-1095) */
+    PF_ERR_NO_DEVICE    = -2,  /* no CUDA device / driver */
+    PF_ERR_CUDA         = -3,  /* a CUDA call failed; see pf_last_error() */
+    PF_ERR_OOM          = -4,
+    PF_ERR_UNSUPPORTED  = -5,  /* e.g. solver = exact / do_exact (out of scope) */
+} pf_status;
+
+/* Storage/arithmetic type of the fields: the reference's compile-time `Real`
+ * (simulation.h:21-25: double unless USE_FLOATS) is a run-time choice here. */
+typedef enum pf_dtype {
+    PF_F32 = 0,
+    PF_F64 = 1,
+} pf_dtype;
+
+/* Same numeric values as Sim_Boundary_Type (simulation.h:27-32). */
+typedef enum pf_boundary {
+    PF_BOUNDARY_PERIODIC       = 0,
+    PF_BOUNDARY_DIRICHLET_ZERO = 1,
+    PF_BOUNDARY_NEUMANN_ZERO   = 2,
+} pf_boundary;
+
+/* Same numeric values as Sim_Solver_Type (simulation.h:34-42). */
+typedef enum pf_solver_type {
+    PF_SOLVER_NONE                  = 0,
+    PF_SOLVER_EXPLICIT_EULER        = 1,  /* "explicit"              */
+    PF_SOLVER_EXPLICIT_RK4          = 2,  /* "explicit-rk4"          */
+    PF_SOLVER_EXPLICIT_RK4_ADAPTIVE = 3,  /* "explicit-rk4-adaptive" */
+    PF_SOLVER_SEMI_IMPLICIT         = 4,  /* "semi-implicit"         */
+    PF_SOLVER_EXACT                 = 5,  /* "exact" - PF_ERR_UNSUPPORTED */
+} pf_solver_type;
+
+/* The numeric content of Sim_Params (simulation.h:83-130) without the host pointers
+ * (stats, temp_maps); field meanings are identical, see config.h:413-479 for the .ini keys. */
+typedef struct pf_params {
+    int32_t solver;              /* pf_solver_type */
+    int32_t nx, ny;              /* GLOBAL grid size */
+    double  time;                /* simulated time at the start of the step (bookkeeping only) */
+    int64_t iter;
+
+    int32_t T_boundary;          /* pf_boundary */
+    int32_t Phi_boundary;
+
+    double L0;                   /* physical side length; dx = L0/nx, dy = L0/ny (simulation.cu:167-168) */
+    double dt;
+    double L;                    /* latent heat */
+    double xi, a, b, alpha, beta;
+    double gamma;                /* theta-scheme weight of the semi-implicit solver */
+    double Tm;
+    double min_dt;               /* lower clamp of the adaptive step (simulation.cu:463) */
+    double S, m0, theta0;        /* anisotropy strength / mode / phase */
+
+    double T_tolerance, Phi_tolerance, corrector_tolerance;
+    int32_t T_max_iters, Phi_max_iters, corrector_max_iters;
+
+    int32_t do_corrector_loop;   /* bool */
+    int32_t do_corrector_guess;  /* bool */
+    int32_t do_stats;            /* bool: fill pf_step_info delta statistics (simulation.cu:1126-1142) */
+    int32_t do_stats_step_residual; /* bool (simulation.cu:979-993) */
+    int32_t do_exact;            /* must be 0 */
+} pf_params;
+
+enum { PF_MAX_STEP_RESIDUALS = 20 };   /* MAX_STEP_RESIDUALS, simulation.h:56 */
+
+/* Per-field delta statistics of one step: Reduce::Stats over (old - new), cuda_reduction.cuh:336-407.
+ * L1 = sum |d| (not divided by N), L2 = sqrt(sum d^2). */
+typedef struct pf_delta_stats {
+    double sum, L1, L2, min, max;
+} pf_delta_stats;
+
+/* What one step did. Superset of what the reference stores in Sim_Stats (simulation.h:57-81):
+ * the reference only LOGS the CG iteration counts (simulation.cu:890,908, "@TODO: stats!" :1006). */
+typedef struct pf_step_info {
+    double  dt_advanced;         /* value sim_step returns (simulation.cu:1155) */
+    int32_t Phi_iters, T_iters;  /* explicit: 1; adaptive: attempts (simulation.cu:488-492); semi-implicit: CG iterations */
+    int32_t Phi_converged, T_converged;
+    double  Phi_error, T_error;  /* adaptive: epsilon_F / epsilon_U of the last attempt; semi-implicit: sqrt(r.r/N) */
+    double  next_tau;            /* adaptive: step proposed for the next call (the reference's function-static, simulation.cu:363,486) */
+    pf_delta_stats Phi_delta, T_delta;      /* valid iff params.do_stats */
+    int32_t step_res_count;                  /* corrector loop residuals, valid iff do_stats_step_residual */
+    pf_delta_stats step_res[PF_MAX_STEP_RESIDUALS];
+} pf_step_info;
+
+/* One rank's slab of a y-decomposed global grid. For a single GPU use
+ * pf_create(), which is the slab {y0 = 0, ny_local = ny, no neighbours}. */
+typedef struct pf_slab {
+    int32_t y0;          /* first owned global row */
+    int32_t ny_local;    /* number of owned rows */
+    int32_t has_lo;      /* a neighbour owns rows below y0 (incl. periodic wrap between first and last rank) */
+    int32_t has_hi;
+    int32_t ghost;       /* ghost rows kept on each side that has a neighbour; >= pf_required_ghost(solver) */
+} pf_slab;
+
+typedef struct pf_solver pf_solver;   /* opaque */
+
+/* ---- library ------------------------------------------------------------------------------- */
+PF_API int          pf_abi_version(void);
+PF_API int          pf_device_count(void);                  /* replaces cuda_one_time_setup device scan, cuda_device.cuh:14-107 */
+PF_API const char*  pf_last_error(const pf_solver* s);      /* s may be NULL: last error of a failed pf_create on this thread */
+PF_API size_t       pf_sizeof_real(int dtype);
+PF_API int          pf_required_ghost(int solver_type);     /* ghost rows one pf_step consumes: 1 / 4 / 5 / 1 */
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+/* Creates a solver bound to CUDA device `device` for an nx x ny grid of `dtype` reals. Owns a stream,
+ * the workspace arena (replaces cache_alloc/cache_free, cuda_alloc.cuh:72-169) and the state the
+ * reference keeps in function statics (adaptive tau simulation.cu:363, corrector parity :936,
+ * conversion staging buffer :1013). */
+PF_API int  pf_create(pf_solver** out, int device, int dtype, int nx, int ny);
+PF_API int  pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global, const pf_slab* slab);
+PF_API void pf_destroy(pf_solver* s);
+PF_API int  pf_reset_state(pf_solver* s);                   /* forget adaptive tau / corrector parity (the reference needs a new process) */
+
+/* ---- fields: replaces sim_realloc (simulation.cu:88-101) ------------------------------------ */
+/* A field is a dense row-major array of rows_alloc x nx reals on the device, index x + y*nx
+ * (simulation.cu:51). Single GPU: rows_alloc = ny. Slab: rows_alloc = ghost_lo + ny_local + ghost_hi
+ * and row 0 of the allocation is global row y0 - ghost_lo. Zero-filled like REALLOC_ZERO. */
+PF_API int  pf_field_alloc(pf_solver* s, void** dev_field);
+PF_API int  pf_field_free(pf_solver* s, void* dev_field);
+PF_API int  pf_field_rows(const pf_solver* s, int* rows_alloc, int* first_owned_row);
+
+/* ---- transfers: replaces sim_modify / sim_modify_float / sim_modify_double (simulation.cu:1010-1067)
+ * `count` reals starting at `dev`; `host_dtype` may differ from the solver dtype, the conversion
+ * then runs on the device exactly like sim_modify_T's staging path. Blocking, like the reference. */
+PF_API int  pf_upload(pf_solver* s, void* dev, const void* host, size_t count, int host_dtype);
+PF_API int  pf_download(pf_solver* s, const void* dev, void* host, size_t count, int host_dtype);
+
+/* ---- the step: replaces sim_step (simulation.cu:1091-1156) ---------------------------------- */
+/* Advances (F, U) by one step of params->solver into (next_F, next_U); all four are device fields of
+ * this solver. Returns after the step has completed on the device (the reference synchronises at
+ * simulation.cu:1153). *info may be NULL. The time advanced is info->dt_advanced (== params->dt for the
+ * fixed-step solvers, the accepted tau for explicit-rk4-adaptive). */
+PF_API int  pf_step(pf_solver* s, const pf_params* params,
+                    const void* F, const void* U, void* next_F, void* next_U, pf_step_info* info);
+
+/* n_steps steps with the host loop's ping-pong (main.cpp:542-558) done inside the library, no host
+ * synchronisation between fixed-dt steps. On return *F_out / *U_out point at whichever of the
+ * two buffer pairs holds the final state; *t_advanced is the summed dt; last_info (may be NULL)
+ * describes the final step. stop_time > 0 stops as soon as params->time + advanced >= stop_time. */
+PF_API int  pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp,
+                   int64_t n_steps, double stop_time,
+                   void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info);
+
+/* Asynchronous variants for host-side pipelining: enqueue on the solver's stream, return immediately.
+ * Fixed-step solvers only (the adaptive solver needs its error norm on the host to answer dt). */
+PF_API int  pf_step_async(pf_solver* s, const pf_params* params,
+                          const void* F, const void* U, void* next_F, void* next_U);
+PF_API int  pf_sync(pf_solver* s);
+PF_API void* pf_stream(pf_solver* s);                        /* cudaStream_t of the solver, for callers that order their own work */
+
+/* ---- single building blocks, exported for parity tests and for the viewer ------------------- */
+/* out = f(sum_i w_i * (F_i, U_i)): the RHS of simulation.cu:145-243 with IS_EULER=false, n_states in 1..4. */
+PF_API int  pf_rhs(pf_solver* s, const pf_params* params, int n_states, const double* weights,
+                   const void* const* Fs, const void* const* Us, void* out_F, void* out_U);
+/* One un-preconditioned CG solve of A x = b (simulation.cu:596-690); which = 0: A_Phi with per-cell factor
+ * `aniso` (simulation.cu:551-578), which = 1: A_T = I - dt*Laplace (simulation.cu:528-549). x0 may be NULL (zero). */
+PF_API int  pf_cg_solve(pf_solver* s, const pf_params* params, int which, const void* aniso,
+                        const void* b, const void* x0, void* x, double tolerance, int max_iters,
+                        int* iters, int* converged, double* error);
+/* Debug maps of calc_debug_values (simulation.cu:245-281): |grad Phi|, |grad T| (undivided differences), g(theta). */
+PF_API int  pf_debug_values(pf_solver* s, const pf_params* params, const void* F, const void* U,
+                            void* grad_F, void* grad_U, void* aniso);
+/* Delta statistics (cuda_stats_delta, cuda_reduction.cuh:391-407) of a - b. */
+PF_API int  pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* out);
+
+/* ---- multi-GPU slabs ----------------------------------------------------- */
+/* Pointers/sizes of the rows a rank must SEND to / RECEIVE from a neighbour before a step:
+ * side 0 = lo (rows below), 1 = hi. `send` = the first/last `ghost` OWNED rows, `recv` = the ghost rows.
+ * The transport (NCCL send/recv or peer copies) is the caller's; rows are contiguous nx*ghost reals. */
+PF_API int  pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, void** recv_ptr, size_t* count);
+
+/* ---- counters -------------------------------------------------------------------------------- */
+PF_API int64_t pf_kernel_launches(const pf_solver* s);      /* kernels launched by this solver so far (bench.py: gpu_launches) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PF_SOLVER_H */
