@@ -1,0 +1,901 @@
+// pf_solver.cu - host side of the C-ABI declared in include/pf_solver.h.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -std=c++17
+//        -Xcompiler -fPIC,-ffp-contract=off -shared   (see __graft_entry__.build()).
+// No CPU fallback exists: every entry point that touches fields needs a CUDA device.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <algorithm>
+
+#include "../../include/pf_solver.h"
+#include "pf_common.cuh"
+#include "pf_fused.cuh"
+#include "pf_general.cuh"
+
+using namespace pf;
+
+// -------------------------------------------------------------------------------------------------------
+enum { PF_SCRATCH_SLOTS = 16 };
+
+struct pf_solver {
+    int device = 0;
+    int dtype = PF_F64;
+    int nx = 0, ny = 0;                 // global grid
+    pf_slab slab = {};
+    int ghost_lo = 0, ghost_hi = 0, rows_alloc = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+
+    void* scratch[PF_SCRATCH_SLOTS] = {};   // workspace arena: whole fields, allocated on first use, freed in pf_destroy
+    void* partials = nullptr;               // 4 x CG_MAX_BLOCKS reals (as doubles)
+    CgState* d_cg = nullptr;                // [2]: Phi solve, T solve
+    StatsPartial* d_stats = nullptr;        // CG_MAX_BLOCKS
+    unsigned long long* d_err = nullptr;    // [2]
+    void* staging = nullptr; size_t staging_bytes = 0;
+
+    // pinned host mirrors
+    unsigned long long* h_err = nullptr;    // [2]
+    CgState* h_cg = nullptr;                // [2]
+    StatsPartial* h_stats = nullptr;        // CG_MAX_BLOCKS
+
+    // state the reference keeps in function statics
+    double adaptive_tau = 0;                // simulation.cu:363
+    int last_num_steps = 0;                 // simulation.cu:936
+
+    unsigned smem_attr_done = 0;            // bit per fused-kernel instance
+    int64_t launches = 0;
+    std::string err;
+
+    size_t real_size() const { return dtype == PF_F64 ? 8 : 4; }
+    size_t field_elems() const { return (size_t) nx * (size_t) rows_alloc; }
+    size_t field_bytes() const { return field_elems() * real_size(); }
+    bool is_full_grid() const { return slab.y0 == 0 && slab.ny_local == ny && !slab.has_lo && !slab.has_hi; }
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(pf_solver* s, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if(s) s->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define PF_CUDA(s, call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) \
+    return fail((s), e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while(0)
+
+#define PF_LAUNCH_CHECK(s) do { (s)->launches++; cudaError_t e_ = cudaGetLastError(); if(e_ != cudaSuccess) \
+    return fail((s), PF_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); } while(0)
+
+static int bind(pf_solver* s)
+{
+    if(!s) return PF_ERR_INVALID;
+    PF_CUDA(s, cudaSetDevice(s->device));
+    return PF_OK;
+}
+
+static int get_scratch(pf_solver* s, int slot, void** out)
+{
+    if(slot < 0 || slot >= PF_SCRATCH_SLOTS) return fail(s, PF_ERR_INVALID, "bad scratch slot %d", slot);
+    if(!s->scratch[slot])
+    {
+        PF_CUDA(s, cudaMalloc(&s->scratch[slot], s->field_bytes()));
+        PF_CUDA(s, cudaMemsetAsync(s->scratch[slot], 0, s->field_bytes(), s->stream));
+    }
+    *out = s->scratch[slot];
+    return PF_OK;
+}
+
+static inline int elementwise_blocks(const pf_solver* s, size_t N, int threads)
+{
+    size_t want = (N + threads - 1) / threads;
+    size_t cap = (size_t) s->sm_count * 16;
+    return (int) std::max<size_t>(1, std::min(want, cap));
+}
+
+// -------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int pf_abi_version(void) { return PF_ABI_VERSION; }
+
+int pf_device_count(void)
+{
+    int n = 0;
+    if(cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char* pf_last_error(const pf_solver* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
+
+size_t pf_sizeof_real(int dtype) { return dtype == PF_F64 ? 8 : (dtype == PF_F32 ? 4 : 0); }
+
+int pf_required_ghost(int solver_type)
+{
+    switch(solver_type)
+    {
+        case PF_SOLVER_EXPLICIT_EULER: return 1;
+        case PF_SOLVER_EXPLICIT_RK4: return 4;
+        case PF_SOLVER_EXPLICIT_RK4_ADAPTIVE: return 5;
+        case PF_SOLVER_SEMI_IMPLICIT: return 1;
+        default: return 0;
+    }
+}
+
+int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global, const pf_slab* slab)
+{
+    if(!out) return fail(nullptr, PF_ERR_INVALID, "pf_create: out is NULL");
+    *out = nullptr;
+    if(dtype != PF_F32 && dtype != PF_F64) return fail(nullptr, PF_ERR_INVALID, "pf_create: bad dtype %d", dtype);
+    if(nx <= 0 || ny_global <= 0) return fail(nullptr, PF_ERR_INVALID, "pf_create: bad grid %dx%d", nx, ny_global);
+    if((long long) nx * (long long) ny_global > 0x7fffffffLL) return fail(nullptr, PF_ERR_INVALID, "pf_create: nx*ny exceeds int32 (the reference's csize, cuda_util.cuh:19)");
+    if(!slab || slab->ny_local <= 0 || slab->y0 < 0 || slab->y0 + slab->ny_local > ny_global || slab->ghost < 0)
+        return fail(nullptr, PF_ERR_INVALID, "pf_create: bad slab");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if(e != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(nullptr, PF_ERR_NO_DEVICE, "no CUDA device: %s (this library has no CPU fallback)", cudaGetErrorString(e)); }
+    if(device < 0 || device >= ndev) return fail(nullptr, PF_ERR_INVALID, "pf_create: device %d out of range (%d devices)", device, ndev);
+
+    pf_solver* s = new pf_solver();
+    s->device = device; s->dtype = dtype; s->nx = nx; s->ny = ny_global; s->slab = *slab;
+    s->ghost_lo = slab->has_lo ? slab->ghost : 0;
+    s->ghost_hi = slab->has_hi ? slab->ghost : 0;
+    s->rows_alloc = s->ghost_lo + slab->ny_local + s->ghost_hi;
+    int rc = PF_OK;
+    auto bail = [&](int code) { g_create_error = s->err; pf_destroy(s); return code; };
+    #define PF_CREATE_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
+        fail(s, e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA); } } while(0)
+    PF_CREATE_CUDA(cudaSetDevice(device));
+    PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
+    PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
+    PF_CREATE_CUDA(cudaMalloc((void**) &s->d_cg, 2 * sizeof(CgState)));
+    PF_CREATE_CUDA(cudaMalloc((void**) &s->d_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
+    PF_CREATE_CUDA(cudaMalloc((void**) &s->d_err, 2 * sizeof(unsigned long long)));
+    PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_err, 2 * sizeof(unsigned long long)));
+    PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_cg, 2 * sizeof(CgState)));
+    PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
+    #undef PF_CREATE_CUDA
+    (void) rc;
+    *out = s;
+    return PF_OK;
+}
+
+int pf_create(pf_solver** out, int device, int dtype, int nx, int ny)
+{
+    pf_slab full = {0, ny, 0, 0, 0};
+    return pf_create_slab(out, device, dtype, nx, ny, &full);
+}
+
+void pf_destroy(pf_solver* s)
+{
+    if(!s) return;
+    cudaSetDevice(s->device);
+    if(s->stream) cudaStreamSynchronize(s->stream);
+    for(int i = 0; i < PF_SCRATCH_SLOTS; i++) if(s->scratch[i]) cudaFree(s->scratch[i]);
+    if(s->partials) cudaFree(s->partials);
+    if(s->d_cg) cudaFree(s->d_cg);
+    if(s->d_stats) cudaFree(s->d_stats);
+    if(s->d_err) cudaFree(s->d_err);
+    if(s->staging) cudaFree(s->staging);
+    if(s->h_err) cudaFreeHost(s->h_err);
+    if(s->h_cg) cudaFreeHost(s->h_cg);
+    if(s->h_stats) cudaFreeHost(s->h_stats);
+    if(s->stream) cudaStreamDestroy(s->stream);
+    cudaGetLastError();
+    delete s;
+}
+
+int pf_reset_state(pf_solver* s)
+{
+    if(!s) return PF_ERR_INVALID;
+    s->adaptive_tau = 0; s->last_num_steps = 0;
+    return PF_OK;
+}
+
+int pf_field_alloc(pf_solver* s, void** dev_field)
+{
+    if(int rc = bind(s)) return rc;
+    if(!dev_field) return fail(s, PF_ERR_INVALID, "pf_field_alloc: NULL out pointer");
+    *dev_field = nullptr;
+    PF_CUDA(s, cudaMalloc(dev_field, s->field_bytes()));
+    PF_CUDA(s, cudaMemsetAsync(*dev_field, 0, s->field_bytes(), s->stream));      // REALLOC_ZERO, simulation.cu:92
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_field_free(pf_solver* s, void* dev_field)
+{
+    if(int rc = bind(s)) return rc;
+    if(dev_field) { PF_CUDA(s, cudaStreamSynchronize(s->stream)); PF_CUDA(s, cudaFree(dev_field)); }
+    return PF_OK;
+}
+
+int pf_field_rows(const pf_solver* s, int* rows_alloc, int* first_owned_row)
+{
+    if(!s) return PF_ERR_INVALID;
+    if(rows_alloc) *rows_alloc = s->rows_alloc;
+    if(first_owned_row) *first_owned_row = s->ghost_lo;
+    return PF_OK;
+}
+
+static int ensure_staging(pf_solver* s, size_t bytes)
+{
+    if(s->staging_bytes < bytes)
+    {
+        if(s->staging) { PF_CUDA(s, cudaStreamSynchronize(s->stream)); PF_CUDA(s, cudaFree(s->staging)); s->staging = nullptr; s->staging_bytes = 0; }
+        PF_CUDA(s, cudaMalloc(&s->staging, bytes));
+        s->staging_bytes = bytes;
+    }
+    return PF_OK;
+}
+
+int pf_upload(pf_solver* s, void* dev, const void* host, size_t count, int host_dtype)
+{
+    if(int rc = bind(s)) return rc;
+    if(!dev || !host) return fail(s, PF_ERR_INVALID, "pf_upload: NULL pointer");
+    if(host_dtype != PF_F32 && host_dtype != PF_F64) return fail(s, PF_ERR_INVALID, "pf_upload: bad host dtype");
+    if(host_dtype == s->dtype)
+        PF_CUDA(s, cudaMemcpyAsync(dev, host, count * s->real_size(), cudaMemcpyHostToDevice, s->stream));
+    else
+    {
+        // host -> staging -> field with the cast on the device, as sim_modify_T does (simulation.cu:1025-1031)
+        size_t hs = pf_sizeof_real(host_dtype);
+        if(int rc = ensure_staging(s, count * hs)) return rc;
+        PF_CUDA(s, cudaMemcpyAsync(s->staging, host, count * hs, cudaMemcpyHostToDevice, s->stream));
+        int blocks = elementwise_blocks(s, count, 256);
+        if(s->dtype == PF_F64) k_convert<double, float><<<blocks, 256, 0, s->stream>>>(count, (const float*) s->staging, (double*) dev);
+        else                   k_convert<float, double><<<blocks, 256, 0, s->stream>>>(count, (const double*) s->staging, (float*) dev);
+        PF_LAUNCH_CHECK(s);
+    }
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_download(pf_solver* s, const void* dev, void* host, size_t count, int host_dtype)
+{
+    if(int rc = bind(s)) return rc;
+    if(!dev || !host) return fail(s, PF_ERR_INVALID, "pf_download: NULL pointer");
+    if(host_dtype != PF_F32 && host_dtype != PF_F64) return fail(s, PF_ERR_INVALID, "pf_download: bad host dtype");
+    if(host_dtype == s->dtype)
+        PF_CUDA(s, cudaMemcpyAsync(host, dev, count * s->real_size(), cudaMemcpyDeviceToHost, s->stream));
+    else
+    {
+        size_t hs = pf_sizeof_real(host_dtype);
+        if(int rc = ensure_staging(s, count * hs)) return rc;
+        int blocks = elementwise_blocks(s, count, 256);
+        if(s->dtype == PF_F64) k_convert<float, double><<<blocks, 256, 0, s->stream>>>(count, (const double*) dev, (float*) s->staging);
+        else                   k_convert<double, float><<<blocks, 256, 0, s->stream>>>(count, (const float*) dev, (double*) s->staging);
+        PF_LAUNCH_CHECK(s);
+        PF_CUDA(s, cudaMemcpyAsync(host, s->staging, count * hs, cudaMemcpyDeviceToHost, s->stream));
+    }
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_sync(pf_solver* s)
+{
+    if(int rc = bind(s)) return rc;
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+void* pf_stream(pf_solver* s) { return s ? (void*) s->stream : nullptr; }
+
+int64_t pf_kernel_launches(const pf_solver* s) { return s ? s->launches : 0; }
+
+int pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, void** recv_ptr, size_t* count)
+{
+    if(!s || !field) return PF_ERR_INVALID;
+    const size_t rs = s->dtype == PF_F64 ? 8 : 4;
+    const int g = s->slab.ghost;
+    char* base = (char*) field;
+    const size_t row_bytes = (size_t) s->nx * rs;
+    if(count) *count = (size_t) g * (size_t) s->nx;
+    if(side == 0)
+    {
+        if(!s->slab.has_lo) { if(send_ptr) *send_ptr = nullptr; if(recv_ptr) *recv_ptr = nullptr; if(count) *count = 0; return PF_OK; }
+        if(recv_ptr) *recv_ptr = base;
+        if(send_ptr) *send_ptr = base + row_bytes * (size_t) s->ghost_lo;
+    }
+    else
+    {
+        if(!s->slab.has_hi) { if(send_ptr) *send_ptr = nullptr; if(recv_ptr) *recv_ptr = nullptr; if(count) *count = 0; return PF_OK; }
+        if(recv_ptr) *recv_ptr = base + row_bytes * (size_t)(s->ghost_lo + s->slab.ny_local);
+        if(send_ptr) *send_ptr = base + row_bytes * (size_t)(s->ghost_lo + s->slab.ny_local - g);
+    }
+    return PF_OK;
+}
+
+} // extern "C"
+
+// -------------------------------------------------------------------------------------------------------
+// Fused explicit step launchers
+// -------------------------------------------------------------------------------------------------------
+template <int SCHEME> struct FusedGeom;                       // extended tile 64 x (TY*R), 512 threads
+template <> struct FusedGeom<SCHEME_EULER> { static constexpr int EW = 64, TY = 8, R = 5; };
+template <> struct FusedGeom<SCHEME_RK4>   { static constexpr int EW = 64, TY = 8, R = 5; };
+template <> struct FusedGeom<SCHEME_RKM>   { static constexpr int EW = 64, TY = 8, R = 4; };
+
+template <typename Real, int SCHEME, bool ANISO>
+static int launch_fused_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bit)
+{
+    using G = FusedGeom<SCHEME>;
+    constexpr int NST = SchemeStages<SCHEME>::value;
+    constexpr int EH = G::TY * G::R;
+    constexpr int TW = G::EW - 2 * NST, TH = EH - 2 * NST;
+    static_assert(TW > 0 && TH > 0, "tile too small for the stage count");
+    using V2 = typename Vec2T<Real>::type;
+    const size_t smem = sizeof(V2) * (size_t) G::EW * EH * (NST > 1 ? 2 : 1);
+    auto kern = k_fused_step<Real, SCHEME, ANISO, G::EW, G::TY, G::R>;
+    if(!(s->smem_attr_done & (1u << inst_bit)))
+    {
+        PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        s->smem_attr_done |= 1u << inst_bit;
+    }
+    const int own_rows = a.own_y1 - a.own_y0;
+    dim3 grid((unsigned)((a.nx + TW - 1) / TW), (unsigned)((own_rows + TH - 1) / TH));
+    dim3 block(G::EW, G::TY);
+    kern<<<grid, block, smem, s->stream>>>(a);
+    PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+template <typename Real>
+static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
+{
+    const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
+    switch(scheme * 2 + (aniso ? 1 : 0))
+    {
+        case 0: return launch_fused_inst<Real, SCHEME_EULER, false>(s, a, base);
+        case 1: return launch_fused_inst<Real, SCHEME_EULER, true>(s, a, base);
+        case 2: return launch_fused_inst<Real, SCHEME_RK4, false>(s, a, base);
+        case 3: return launch_fused_inst<Real, SCHEME_RK4, true>(s, a, base);
+        case 4: return launch_fused_inst<Real, SCHEME_RKM, false>(s, a, base);
+        default: return launch_fused_inst<Real, SCHEME_RKM, true>(s, a, base);
+    }
+}
+
+template <typename Real>
+static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, const void* F, const void* U, void* nF, void* nU)
+{
+    FusedArgs<Real> a;
+    memset(&a, 0, sizeof a);
+    a.F = (const Real*) F; a.U = (const Real*) U; a.out_F = (Real*) nF; a.out_U = (Real*) nU;
+    a.nx = s->nx; a.ny_global = s->ny;
+    a.row0 = s->slab.y0 - s->ghost_lo; a.rows_local = s->rows_alloc;
+    a.own_y0 = s->slab.y0; a.own_y1 = s->slab.y0 + s->slab.ny_local;
+    a.bc = p.Phi_boundary;
+    a.wrap_y = (p.Phi_boundary == PF_BOUNDARY_PERIODIC && !s->slab.has_lo && !s->slab.has_hi) ? 1 : 0;
+    a.k = make_consts<Real>(p);
+    a.err_bits = s->d_err;
+    return a;
+}
+
+static bool fused_eligible(const pf_solver* s, const pf_params& p)
+{
+    if(p.Phi_boundary != p.T_boundary) return false;                 // mixed boundary types: general path
+    if(p.Phi_boundary == PF_BOUNDARY_PERIODIC && (s->slab.has_lo != s->slab.has_hi)) return false;
+    return true;
+}
+
+// -------------------------------------------------------------------------------------------------------
+// General per-stage path (any boundary mix; single GPU full grid only)
+// -------------------------------------------------------------------------------------------------------
+template <typename Real>
+static int launch_rhs_general(pf_solver* s, const pf_params& p, bool is_euler, int n_states, const Real* w,
+                              const Real* const* Fs, const Real* const* Us, Real* out_F, Real* out_U)
+{
+    BlendArgs<Real> b; memset(&b, 0, sizeof b);
+    b.n_states = n_states;
+    for(int i = 0; i < n_states; i++) { b.w[i] = w[i]; b.F[i] = Fs[i]; b.U[i] = Us[i]; }
+    KConsts<Real> k = make_consts<Real>(p);
+    dim3 block(32, 8), grid((unsigned)((s->nx + 31) / 32), (unsigned)((s->ny + 7) / 8));
+    if(p.S != 0) k_rhs_general<Real, true><<<grid, block, 0, s->stream>>>(b, k, s->nx, s->ny, p.Phi_boundary, p.T_boundary, is_euler ? 1 : 0, out_F, out_U);
+    else         k_rhs_general<Real, false><<<grid, block, 0, s->stream>>>(b, k, s->nx, s->ny, p.Phi_boundary, p.T_boundary, is_euler ? 1 : 0, out_F, out_U);
+    PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+// explicit_solver_euler_step_based: reference simulation.cu:283-311.
+template <typename Real>
+static int euler_step_based(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU, pf_step_info* info)
+{
+    if(U == U_base)
+    {
+        if(fused_eligible(s, p))
+        {
+            FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+            if(int rc = launch_fused<Real>(s, SCHEME_EULER, p.S != 0, a)) return rc;
+        }
+        else
+        {
+            if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "mixed boundary types are single-GPU only");
+            Real one = 1; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
+            if(int rc = launch_rhs_general<Real>(s, p, true, 1, &one, Fs, Us, nF, nU)) return rc;
+        }
+    }
+    else
+    {
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "the corrector loop is single-GPU only");
+        void *dF, *dU;
+        if(int rc = get_scratch(s, 0, &dF)) return rc;
+        if(int rc = get_scratch(s, 1, &dU)) return rc;
+        Real one = 1; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
+        if(int rc = launch_rhs_general<Real>(s, p, false, 1, &one, Fs, Us, (Real*) dF, (Real*) dU)) return rc;
+        size_t N = s->field_elems();
+        k_euler_corrector_axpy<Real><<<elementwise_blocks(s, N, 256), 256, 0, s->stream>>>(N, (Real) p.dt, F, U_base, (const Real*) dF, (const Real*) dU, nF, nU);
+        PF_LAUNCH_CHECK(s);
+    }
+    if(info) { info->Phi_iters = 1; info->T_iters = 1; }
+    return PF_OK;
+}
+
+// explicit_solver_rk4_step: reference simulation.cu:313-348.
+template <typename Real>
+static int rk4_step(pf_solver* s, const pf_params& p, const Real* F, const Real* U, Real* nF, Real* nU, pf_step_info* info)
+{
+    const Real dt = (Real) p.dt;
+    if(fused_eligible(s, p))
+    {
+        FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+        a.w[0] = dt / 2; a.w[1] = dt / 2; a.w[2] = dt; a.w[3] = dt / 6;
+        if(int rc = launch_fused<Real>(s, SCHEME_RK4, p.S != 0, a)) return rc;
+    }
+    else
+    {
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "mixed boundary types are single-GPU only");
+        Real* k[8];
+        for(int i = 0; i < 8; i++) { void* q; if(int rc = get_scratch(s, i, &q)) return rc; k[i] = (Real*) q; }
+        Real *k1F = k[0], *k2F = k[1], *k3F = k[2], *k4F = k[3], *k1U = k[4], *k2U = k[5], *k3U = k[6], *k4U = k[7];
+        { Real w[1] = {1}; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
+          if(int rc = launch_rhs_general<Real>(s, p, false, 1, w, Fs, Us, k1F, k1U)) return rc; }
+        { Real w[2] = {1, dt / 2}; const Real* Fs[2] = {F, k1F}; const Real* Us[2] = {U, k1U};
+          if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k2F, k2U)) return rc; }
+        { Real w[2] = {1, dt / 2}; const Real* Fs[2] = {F, k2F}; const Real* Us[2] = {U, k2U};
+          if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k3F, k3U)) return rc; }
+        { Real w[2] = {1, dt}; const Real* Fs[2] = {F, k3F}; const Real* Us[2] = {U, k3U};
+          if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k4F, k4U)) return rc; }
+        size_t N = s->field_elems();
+        int blocks = elementwise_blocks(s, N, 256);
+        k_rk4_combine<Real><<<blocks, 256, 0, s->stream>>>(N, dt / 6, F, k1F, k2F, k3F, k4F, nF); PF_LAUNCH_CHECK(s);
+        k_rk4_combine<Real><<<blocks, 256, 0, s->stream>>>(N, dt / 6, U, k1U, k2U, k3U, k4U, nU); PF_LAUNCH_CHECK(s);
+    }
+    if(info) { info->Phi_iters = 1; info->T_iters = 1; }
+    return PF_OK;
+}
+
+// Decodes the atomicMax'ed bit patterns of the two error norms.
+template <typename Real> static Real decode_err(unsigned long long bits);
+template <> double decode_err<double>(unsigned long long bits) { double d; memcpy(&d, &bits, 8); return d; }
+template <> float decode_err<float>(unsigned long long bits) { uint32_t u = (uint32_t) bits; float f; memcpy(&f, &u, 4); return f; }
+
+static inline double pf_pow(double a, double b) { return pow(a, b); }
+static inline float pf_pow(float a, float b) { return powf(a, b); }
+
+// explicit_solver_rk4_adaptive_step (Runge-Kutta-Merson): reference simulation.cu:350-497.
+// The step-size controller runs on the host in Real arithmetic with the same libm pow as the reference's host code.
+template <typename Real>
+static int rk4_adaptive_step(pf_solver* s, const pf_params& p, const Real* F, const Real* U, Real* nF, Real* nU, pf_step_info* info, double* dt_out)
+{
+    if(s->adaptive_tau <= 0) s->adaptive_tau = (double)(Real) p.dt;        // :363-365
+    Real tau = (Real) s->adaptive_tau;
+    Real epsilon_F = 0, epsilon_U = 0;
+    const bool fused = fused_eligible(s, p);
+    Real* k[10] = {};
+    size_t N = s->field_elems();
+    if(!fused)
+    {
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "mixed boundary types are single-GPU only");
+        for(int i = 0; i < 10; i++) { void* q; if(int rc = get_scratch(s, i, &q)) return rc; k[i] = (Real*) q; }
+        Real w[1] = {1}; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
+        if(int rc = launch_rhs_general<Real>(s, p, false, 1, w, Fs, Us, k[0], k[5])) return rc;      // k1, :386
+    }
+    bool converged = false;
+    int i = 0;
+    int max_iters = std::max(std::max(p.T_max_iters, p.Phi_max_iters), 1);  // :390
+    Real used_tau = tau;
+    for(; i < max_iters && !converged; i++)
+    {
+        PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
+        if(fused)
+        {
+            FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+            a.w[0] = tau / 3; a.w[1] = tau / 6; a.w[2] = tau / 8; a.w[3] = tau * 3 / 8;
+            a.w[4] = tau / 2; a.w[5] = -tau * 3 / 2; a.w[6] = tau * 2; a.w[7] = tau / 6;
+            if(int rc = launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a)) return rc;
+        }
+        else
+        {
+            Real *k1F = k[0], *k2F = k[1], *k3F = k[2], *k4F = k[3], *k5F = k[4], *k1U = k[5], *k2U = k[6], *k3U = k[7], *k4U = k[8], *k5U = k[9];
+            { Real w[2] = {1, tau / 3}; const Real* Fs[2] = {F, k1F}; const Real* Us[2] = {U, k1U};
+              if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k2F, k2U)) return rc; }
+            { Real w[3] = {1, tau / 6, tau / 6}; const Real* Fs[3] = {F, k1F, k2F}; const Real* Us[3] = {U, k1U, k2U};
+              if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k3F, k3U)) return rc; }
+            { Real w[3] = {1, tau / 8, tau * 3 / 8}; const Real* Fs[3] = {F, k1F, k3F}; const Real* Us[3] = {U, k1U, k3U};
+              if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k4F, k4U)) return rc; }
+            { Real w[4] = {1, tau / 2, -tau * 3 / 2, tau * 2}; const Real* Fs[4] = {F, k1F, k3F, k4F}; const Real* Us[4] = {U, k1U, k3U, k4U};
+              if(int rc = launch_rhs_general<Real>(s, p, false, 4, w, Fs, Us, k5F, k5U)) return rc; }
+            int blocks = elementwise_blocks(s, N, 256);
+            k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1F, k3F, k4F, k5F, s->d_err + 0); PF_LAUNCH_CHECK(s);
+            k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1U, k3U, k4U, k5U, s->d_err + 1); PF_LAUNCH_CHECK(s);
+        }
+        PF_CUDA(s, cudaMemcpyAsync(s->h_err, s->d_err, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        PF_CUDA(s, cudaStreamSynchronize(s->stream));
+        Real max_F = decode_err<Real>(s->h_err[0]);
+        Real max_U = decode_err<Real>(s->h_err[1]);
+        epsilon_F = tau / 3 * max_F;                                        // :437-438
+        epsilon_U = tau / 3 * max_U;
+
+        if((double) epsilon_F < p.Phi_tolerance && (double) epsilon_U < p.T_tolerance) converged = true;   // :456
+        double e_max = (double)(epsilon_F > epsilon_U ? epsilon_F : epsilon_U);
+        Real epsilon = (Real)(e_max > 1e-20 ? e_max : 1e-20);               // :459
+        double d_min = p.Phi_tolerance < p.T_tolerance ? p.Phi_tolerance : p.T_tolerance;
+        Real delta = (Real)(d_min > 1e-20 ? d_min : 1e-20);                 // :460
+        used_tau = tau;
+        tau = pf_pow(delta / epsilon, (Real) 0.2) * 4 / 5 * tau;            // :462
+        tau = (Real)((double) tau > p.min_dt ? (double) tau : p.min_dt);    // :463
+        if((double) tau <= p.min_dt && (double) used_tau <= p.min_dt) break;   // :466
+    }
+    if(!fused)
+    {
+        int blocks = elementwise_blocks(s, N, 256);
+        k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, F, k[0], k[3], k[4], nF); PF_LAUNCH_CHECK(s);
+        k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, U, k[5], k[8], k[9], nU); PF_LAUNCH_CHECK(s);
+    }
+    s->adaptive_tau = (double) tau;                                         // :486
+    if(info)
+    {
+        info->Phi_iters = i; info->T_iters = i;
+        info->Phi_converged = converged; info->T_converged = converged;
+        info->Phi_error = (double) epsilon_F; info->T_error = (double) epsilon_U;
+        info->next_tau = (double) tau;
+    }
+    *dt_out = (double) used_tau;
+    return PF_OK;
+}
+
+// -------------------------------------------------------------------------------------------------------
+// Semi-implicit solver
+// -------------------------------------------------------------------------------------------------------
+static inline int cg_blocks(const pf_solver* s, int nx, int ny)
+{
+    int segs = (nx + CG_THREADS - 1) / CG_THREADS;
+    long long items = (long long) segs * ny;
+    long long want = std::min<long long>(items, (long long) s->sm_count * 4);
+    return (int) std::max<long long>(1, std::min<long long>(want, CG_MAX_BLOCKS));
+}
+
+// conjugate_gradient_solve: reference simulation.cu:596-690. All scalars stay on the device; `which` selects the CgState slot.
+template <typename Real>
+static int cg_solve_device(pf_solver* s, const CgMatrix<Real>& A, Real* x, const Real* b, const Real* x0, Real tolerance, int max_iters,
+                           Real* r, Real* pv, Real* Ap, int slot)
+{
+    const int nx = A.nx, ny = A.ny;
+    const size_t N = (size_t) nx * (size_t) ny;
+    const int blocks = cg_blocks(s, nx, ny);
+    Real* P = (Real*) s->partials;
+    Real* rrP[2] = {P, P + CG_MAX_BLOCKS};
+    Real* pApP = P + 2 * CG_MAX_BLOCKS;
+    CgState* st = s->d_cg + slot;
+    const Real epsilon = (Real) 1.0e-12;                                    // simulation.cu:882
+    const Real sst = tolerance * tolerance * (Real)(int) N;                 // :608
+    k_cg_init<Real><<<blocks, CG_THREADS, 0, s->stream>>>(A, x0, b, x, r, pv, rrP[0], st, max_iters); PF_LAUNCH_CHECK(s);
+    for(int it = 0; it < max_iters; it++)
+    {
+        k_cg_spmv<Real><<<blocks, CG_THREADS, 0, s->stream>>>(A, pv, Ap, pApP, st); PF_LAUNCH_CHECK(s);
+        k_cg_update<Real><<<blocks, CG_THREADS, 0, s->stream>>>(N, epsilon, x, r, pv, Ap, rrP[it & 1], pApP, rrP[(it + 1) & 1], blocks, st); PF_LAUNCH_CHECK(s);
+        k_cg_pupdate<Real><<<blocks, CG_THREADS, 0, s->stream>>>(N, epsilon, sst, r, pv, rrP[it & 1], rrP[(it + 1) & 1], blocks, st, it); PF_LAUNCH_CHECK(s);
+    }
+    if(max_iters <= 0) { k_cg_finalize<Real><<<1, CG_THREADS, 0, s->stream>>>(rrP[0], blocks, st); PF_LAUNCH_CHECK(s); }
+    return PF_OK;
+}
+
+template <typename Real>
+static CgMatrix<Real> make_matrix(const pf_params& p, int which, const Real* factor)
+{
+    CgMatrix<Real> A; memset(&A, 0, sizeof A);
+    const Real dt = (Real) p.dt, dx = (Real) p.L0 / p.nx, dy = (Real) p.L0 / p.ny;
+    A.which = which; A.factor = factor; A.nx = p.nx; A.ny = p.ny;
+    if(which == 0)
+    {
+        A.C_minus_one = 2 * dt / (dx * dx) + 2 * dt / (dy * dy);          // simulation.cu:774-776
+        A.X = -dt / (dx * dx);
+        A.Y = -dt / (dy * dy);
+        A.boundary = p.Phi_boundary;
+    }
+    else
+    {
+        A.C = 1 + 2 * dt / (dx * dx) + 2 * dt / (dy * dy);                // simulation.cu:783-787
+        A.R = -dt / (dx * dx); A.Lc = -dt / (dx * dx);
+        A.Uc = -dt / (dy * dy); A.D = -dt / (dy * dy);
+        A.boundary = p.T_boundary;
+    }
+    return A;
+}
+
+// semi_implicit_solver_step_based: reference simulation.cu:732-926 (without the do_debug back-substitution).
+template <typename Real>
+static int semi_implicit_step_based(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU)
+{
+    if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "the semi-implicit solver is single-GPU only in this version");
+    void* q[6];
+    for(int i = 0; i < 6; i++) if(int rc = get_scratch(s, 2 + i, &q[i])) return rc;     // slots 0,1 are the corrector's temporaries
+    Real *b_F = (Real*) q[0], *b_U = (Real*) q[1], *aniso = (Real*) q[2], *r = (Real*) q[3], *pv = (Real*) q[4], *Ap = (Real*) q[5];
+    KConsts<Real> k = make_consts<Real>(p);
+    dim3 block(32, 8), grid((unsigned)((s->nx + 31) / 32), (unsigned)((s->ny + 7) / 8));
+    if(p.S != 0) k_si_prepare<Real, true><<<grid, block, 0, s->stream>>>(F, U, b_F, aniso, s->nx, s->ny, p.Phi_boundary, p.T_boundary, k);
+    else         k_si_prepare<Real, false><<<grid, block, 0, s->stream>>>(F, U, b_F, aniso, s->nx, s->ny, p.Phi_boundary, p.T_boundary, k);
+    PF_LAUNCH_CHECK(s);
+
+    CgMatrix<Real> A_F = make_matrix<Real>(p, 0, aniso);
+    if(int rc = cg_solve_device<Real>(s, A_F, nF, b_F, F, (Real) p.Phi_tolerance, p.Phi_max_iters, r, pv, Ap, 0)) return rc;   // :881-888
+
+    const size_t N = s->field_elems();
+    const Real dt = (Real) p.dt, gamma = (Real) p.gamma;
+    k_si_bU<Real><<<elementwise_blocks(s, N, 256), 256, 0, s->stream>>>(N, (Real) p.L, dt * (1 - gamma), U_base, F, nF, b_U);   // :893-899
+    PF_LAUNCH_CHECK(s);
+
+    CgMatrix<Real> A_U = make_matrix<Real>(p, 1, nullptr);
+    if(int rc = cg_solve_device<Real>(s, A_U, nU, b_U, U, (Real) p.T_tolerance, p.T_max_iters, r, pv, Ap, 1)) return rc;       // :901-906
+    return PF_OK;
+}
+
+template <typename Real>
+static int stats_delta_device(pf_solver* s, const Real* a, const Real* b, pf_delta_stats* out)
+{
+    const size_t N = s->field_elems();
+    int blocks = std::min<int>(CG_MAX_BLOCKS, elementwise_blocks(s, N, CG_THREADS));
+    k_stats_delta<Real><<<blocks, CG_THREADS, 0, s->stream>>>(N, a, b, s->d_stats); PF_LAUNCH_CHECK(s);
+    PF_CUDA(s, cudaMemcpyAsync(s->h_stats, s->d_stats, blocks * sizeof(StatsPartial), cudaMemcpyDeviceToHost, s->stream));
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    Real sum = 0, L1 = 0, L2 = 0, mn = (Real) INFINITY, mx = -(Real) INFINITY;   // fixed order: bit-stable
+    for(int i = 0; i < blocks; i++)
+    {
+        sum += (Real) s->h_stats[i].sum; L1 += (Real) s->h_stats[i].L1; L2 += (Real) s->h_stats[i].L2;
+        mn = std::min(mn, (Real) s->h_stats[i].mn); mx = std::max(mx, (Real) s->h_stats[i].mx);
+    }
+    out->sum = (double) sum; out->L1 = (double) L1; out->L2 = (double)(Real) sqrt((double) L2);
+    out->min = (double) mn; out->max = (double) mx;
+    return PF_OK;
+}
+
+// semi_implicit_and_euler_solver_step_corrector: reference simulation.cu:928-1008.
+template <typename Real>
+static int step_corrector(pf_solver* s, const pf_params& p, const Real* F, const Real* U, Real* nF, Real* nU, pf_step_info* info)
+{
+    size_t max_iters = (size_t) std::max(0, p.corrector_max_iters);
+    if(!p.do_corrector_loop) max_iters = 0;
+    if(max_iters == 0 && p.do_stats_step_residual) max_iters = 1;
+
+    Real* steps_F[2]; Real* steps_U[2];
+    Real *tF = nullptr, *tU = nullptr;
+    const bool need_temp = max_iters > 0 || (s->last_num_steps % 2) != 0;
+    if(need_temp)
+    {
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "the corrector loop is single-GPU only");
+        void* q; if(int rc = get_scratch(s, 10, &q)) return rc; tF = (Real*) q;
+        if(int rc = get_scratch(s, 11, &q)) return rc; tU = (Real*) q;
+    }
+    if(s->last_num_steps % 2 == 0) { steps_F[0] = nF; steps_U[0] = nU; steps_F[1] = tF; steps_U[1] = tU; }
+    else                           { steps_F[1] = nF; steps_U[1] = nU; steps_F[0] = tF; steps_U[0] = tU; }
+
+    const bool euler = p.solver == PF_SOLVER_EXPLICIT_EULER;
+    if(euler) { if(int rc = euler_step_based<Real>(s, p, F, U, U, steps_F[0], steps_U[0], info)) return rc; }
+    else      { if(int rc = semi_implicit_step_based<Real>(s, p, F, U, U, steps_F[0], steps_U[0])) return rc; }
+    for(size_t k = 0; k < max_iters; k++)
+    {
+        int curr = (int)(k % 2), next = (int)((k + 1) % 2);
+        if(euler) { if(int rc = euler_step_based<Real>(s, p, F, steps_U[curr], U, steps_F[next], steps_U[next], info)) return rc; }
+        else      { if(int rc = semi_implicit_step_based<Real>(s, p, F, steps_U[curr], U, steps_F[next], steps_U[next])) return rc; }
+        if(p.do_stats_step_residual && info && k < PF_MAX_STEP_RESIDUALS)
+        {
+            if(int rc = stats_delta_device<Real>(s, steps_F[curr], steps_F[next], &info->step_res[k])) return rc;
+            info->step_res_count = (int) max_iters;
+        }
+        s->last_num_steps = (int) k;                                        // :995
+    }
+    int final_step = ((s->last_num_steps % 2) + 2) % 2;                     // :999
+    if(steps_F[final_step] != nF)
+    {
+        PF_CUDA(s, cudaMemcpyAsync(nF, steps_F[final_step], s->field_bytes(), cudaMemcpyDeviceToDevice, s->stream));
+        PF_CUDA(s, cudaMemcpyAsync(nU, steps_U[final_step], s->field_bytes(), cudaMemcpyDeviceToDevice, s->stream));
+    }
+    return PF_OK;
+}
+
+// sim_step: reference simulation.cu:1091-1156. `sync` = return only when the device is done (the reference always does).
+template <typename Real>
+static int step_impl(pf_solver* s, const pf_params& p, const void* F_, const void* U_, void* nF_, void* nU_, pf_step_info* info, bool sync)
+{
+    const Real* F = (const Real*) F_; const Real* U = (const Real*) U_; Real* nF = (Real*) nF_; Real* nU = (Real*) nU_;
+    pf_step_info local; if(!info) info = &local;
+    memset(info, 0, sizeof *info);
+    double dt = 0;
+    switch(p.solver)
+    {
+        case PF_SOLVER_SEMI_IMPLICIT:
+        case PF_SOLVER_EXPLICIT_EULER:
+            if(int rc = step_corrector<Real>(s, p, F, U, nF, nU, info)) return rc;
+            dt = p.dt; break;
+        case PF_SOLVER_EXPLICIT_RK4:
+            if(int rc = rk4_step<Real>(s, p, F, U, nF, nU, info)) return rc;
+            dt = p.dt; break;
+        case PF_SOLVER_EXPLICIT_RK4_ADAPTIVE:
+            if(int rc = rk4_adaptive_step<Real>(s, p, F, U, nF, nU, info, &dt)) return rc;
+            break;
+        case PF_SOLVER_EXACT:
+            return fail(s, PF_ERR_UNSUPPORTED, "solver = exact is out of scope (reference marks it 'slightly broken', simulation.h:17)");
+        default:
+            return fail(s, PF_ERR_INVALID, "unknown solver %d", p.solver);
+    }
+    if(p.do_stats)
+    {
+        if(int rc = stats_delta_device<Real>(s, F, nF, &info->Phi_delta)) return rc;       // :1128-1129
+        if(int rc = stats_delta_device<Real>(s, U, nU, &info->T_delta)) return rc;
+    }
+    if(p.solver == PF_SOLVER_SEMI_IMPLICIT && sync)
+    {
+        PF_CUDA(s, cudaMemcpyAsync(s->h_cg, s->d_cg, 2 * sizeof(CgState), cudaMemcpyDeviceToHost, s->stream));
+        PF_CUDA(s, cudaStreamSynchronize(s->stream));
+        const double N = (double) s->nx * (double) s->ny;
+        info->Phi_iters = s->h_cg[0].iters; info->T_iters = s->h_cg[1].iters;
+        info->Phi_converged = s->h_cg[0].iters != p.Phi_max_iters; info->T_converged = s->h_cg[1].iters != p.T_max_iters;
+        info->Phi_error = (double)(Real) sqrt((double)(Real)((Real) s->h_cg[0].rr / (Real) N));
+        info->T_error = (double)(Real) sqrt((double)(Real)((Real) s->h_cg[1].rr / (Real) N));
+    }
+    else if(sync)
+        PF_CUDA(s, cudaStreamSynchronize(s->stream));                       // :1153
+    info->dt_advanced = dt;
+    return PF_OK;
+}
+
+static int check_step_args(pf_solver* s, const pf_params* p, const void* F, const void* U, const void* nF, const void* nU)
+{
+    if(!p || !F || !U || !nF || !nU) return fail(s, PF_ERR_INVALID, "pf_step: NULL argument");
+    if(p->nx != s->nx || p->ny != s->ny)                                    // simulation.cu:1094-1095
+        return fail(s, PF_ERR_INVALID, "Bad sizes provided: params %dx%d, solver %dx%d", p->nx, p->ny, s->nx, s->ny);
+    if(p->do_exact) return fail(s, PF_ERR_UNSUPPORTED, "do_exact is out of scope");
+    if(F == nF || U == nU) return fail(s, PF_ERR_INVALID, "pf_step: in-place stepping is not supported");
+    for(int b : {p->Phi_boundary, p->T_boundary})
+        if(b < PF_BOUNDARY_PERIODIC || b > PF_BOUNDARY_NEUMANN_ZERO) return fail(s, PF_ERR_INVALID, "bad boundary type %d", b);
+    if(!s->is_full_grid() && s->slab.ghost < pf_required_ghost(p->solver))
+        return fail(s, PF_ERR_INVALID, "slab ghost depth %d < %d required by solver %d", s->slab.ghost, pf_required_ghost(p->solver), p->solver);
+    return PF_OK;
+}
+
+extern "C" {
+
+int pf_step(pf_solver* s, const pf_params* params, const void* F, const void* U, void* next_F, void* next_U, pf_step_info* info)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    return s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, info, true)
+                              : step_impl<float>(s, *params, F, U, next_F, next_U, info, true);
+}
+
+int pf_step_async(pf_solver* s, const pf_params* params, const void* F, const void* U, void* next_F, void* next_U)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    if(params->solver == PF_SOLVER_EXPLICIT_RK4_ADAPTIVE) return fail(s, PF_ERR_UNSUPPORTED, "pf_step_async: the adaptive solver answers dt on the host");
+    if(params->do_stats || params->do_stats_step_residual) return fail(s, PF_ERR_UNSUPPORTED, "pf_step_async: statistics need the host");
+    return s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
+                              : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
+}
+
+int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
+           void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, F_tmp, U_tmp)) return rc;
+    pf_params p = *params;
+    void *cF = F, *cU = U, *nF = F_tmp, *nU = U_tmp;
+    double t = params->time;
+    int64_t i = 0;
+    // fixed-dt solvers without statistics never need the host between steps: enqueue everything, synchronise once
+    const bool async_ok = p.solver != PF_SOLVER_EXPLICIT_RK4_ADAPTIVE && !p.do_stats && !p.do_stats_step_residual;
+    for(; i < n_steps; i++)
+    {
+        if(stop_time > 0 && stop_time - t < 1e-16) break;                  // main.cpp:525
+        p.iter = params->iter + i; p.time = t;
+        const bool last = (i + 1 == n_steps) || (stop_time > 0 && stop_time - (t + p.dt) < 1e-16 && async_ok);
+        pf_step_info info;
+        int rc = s->dtype == PF_F64 ? step_impl<double>(s, p, cF, cU, nF, nU, &info, !async_ok || last)
+                                    : step_impl<float>(s, p, cF, cU, nF, nU, &info, !async_ok || last);
+        if(rc) return rc;
+        t += info.dt_advanced;
+        if(last_info) *last_info = info;
+        std::swap(cF, nF); std::swap(cU, nU);
+    }
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    if(F_out) *F_out = cF;
+    if(U_out) *U_out = cU;
+    if(steps_done) *steps_done = i;
+    if(t_advanced) *t_advanced = t - params->time;
+    return PF_OK;
+}
+
+int pf_rhs(pf_solver* s, const pf_params* params, int n_states, const double* weights, const void* const* Fs, const void* const* Us, void* out_F, void* out_U)
+{
+    if(int rc = bind(s)) return rc;
+    if(!params || !weights || !Fs || !Us || !out_F || !out_U || n_states < 1 || n_states > 4) return fail(s, PF_ERR_INVALID, "pf_rhs: bad arguments");
+    if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "pf_rhs is single-GPU only");
+    if(params->nx != s->nx || params->ny != s->ny) return fail(s, PF_ERR_INVALID, "pf_rhs: size mismatch");
+    int rc;
+    if(s->dtype == PF_F64)
+    {
+        double w[4]; for(int i = 0; i < n_states; i++) w[i] = weights[i];
+        rc = launch_rhs_general<double>(s, *params, false, n_states, w, (const double* const*) Fs, (const double* const*) Us, (double*) out_F, (double*) out_U);
+    }
+    else
+    {
+        float w[4]; for(int i = 0; i < n_states; i++) w[i] = (float) weights[i];
+        rc = launch_rhs_general<float>(s, *params, false, n_states, w, (const float* const*) Fs, (const float* const*) Us, (float*) out_F, (float*) out_U);
+    }
+    if(rc) return rc;
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_cg_solve(pf_solver* s, const pf_params* params, int which, const void* aniso, const void* b, const void* x0, void* x,
+                double tolerance, int max_iters, int* iters, int* converged, double* error)
+{
+    if(int rc = bind(s)) return rc;
+    if(!params || !b || !x || (which != 0 && which != 1) || (which == 0 && !aniso)) return fail(s, PF_ERR_INVALID, "pf_cg_solve: bad arguments");
+    if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "pf_cg_solve is single-GPU only");
+    if(params->nx != s->nx || params->ny != s->ny) return fail(s, PF_ERR_INVALID, "pf_cg_solve: size mismatch");
+    void* q[3];
+    for(int i = 0; i < 3; i++) if(int rc = get_scratch(s, 5 + i, &q[i])) return rc;
+    int rc;
+    if(s->dtype == PF_F64)
+    {
+        CgMatrix<double> A = make_matrix<double>(*params, which, (const double*) aniso);
+        rc = cg_solve_device<double>(s, A, (double*) x, (const double*) b, (const double*) x0, tolerance, max_iters, (double*) q[0], (double*) q[1], (double*) q[2], which);
+    }
+    else
+    {
+        CgMatrix<float> A = make_matrix<float>(*params, which, (const float*) aniso);
+        rc = cg_solve_device<float>(s, A, (float*) x, (const float*) b, (const float*) x0, (float) tolerance, max_iters, (float*) q[0], (float*) q[1], (float*) q[2], which);
+    }
+    if(rc) return rc;
+    PF_CUDA(s, cudaMemcpyAsync(s->h_cg, s->d_cg, 2 * sizeof(CgState), cudaMemcpyDeviceToHost, s->stream));
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    const double N = (double) s->nx * (double) s->ny;
+    if(iters) *iters = s->h_cg[which].iters;
+    if(converged) *converged = s->h_cg[which].iters != max_iters;
+    if(error) *error = s->dtype == PF_F64 ? sqrt(s->h_cg[which].rr / N) : (double) sqrtf((float) s->h_cg[which].rr / (float) N);
+    return PF_OK;
+}
+
+int pf_debug_values(pf_solver* s, const pf_params* params, const void* F, const void* U, void* grad_F, void* grad_U, void* aniso)
+{
+    if(int rc = bind(s)) return rc;
+    if(!params || !F || !U || !grad_F || !grad_U || !aniso) return fail(s, PF_ERR_INVALID, "pf_debug_values: NULL argument");
+    if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "pf_debug_values is single-GPU only");
+    dim3 block(32, 8), grid((unsigned)((s->nx + 31) / 32), (unsigned)((s->ny + 7) / 8));
+    if(s->dtype == PF_F64)
+        k_debug_values<double><<<grid, block, 0, s->stream>>>((const double*) F, (const double*) U, (double*) grad_F, (double*) grad_U, (double*) aniso,
+                                                                s->nx, s->ny, params->Phi_boundary, params->T_boundary, make_consts<double>(*params));
+    else
+        k_debug_values<float><<<grid, block, 0, s->stream>>>((const float*) F, (const float*) U, (float*) grad_F, (float*) grad_U, (float*) aniso,
+                                                               s->nx, s->ny, params->Phi_boundary, params->T_boundary, make_consts<float>(*params));
+    PF_LAUNCH_CHECK(s);
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* out)
+{
+    if(int rc = bind(s)) return rc;
+    if(!a || !b || !out) return fail(s, PF_ERR_INVALID, "pf_stats_delta: NULL argument");
+    return s->dtype == PF_F64 ? stats_delta_device<double>(s, (const double*) a, (const double*) b, out)
+                              : stats_delta_device<float>(s, (const float*) a, (const float*) b, out);
+}
+
+} // extern "C"

@@ -1,0 +1,212 @@
+"""ctypes binding of the C-ABI in include/pf_solver.h (bachelors_b200/libpfsolver.so).
+
+There is no CPU fallback: if the CUDA library is missing or no device is present, this raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._abi import (PF_ABI_VERSION, PF_F32, PF_F64, PF_OK, pf_params, pf_step_info, pf_delta_stats, pf_slab)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpfsolver.so")
+
+# every symbol include/pf_solver.h declares
+EXPORTS = [
+    "pf_abi_version", "pf_device_count", "pf_last_error", "pf_sizeof_real", "pf_required_ghost",
+    "pf_create", "pf_create_slab", "pf_destroy", "pf_reset_state",
+    "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download",
+    "pf_step", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
+    "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
+]
+
+
+class PfError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"pf_solver error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Loads libpfsolver.so. Fails loudly when the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(nvcc, sm_100a). This package has no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, dbl, sz = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_size_t
+    P = C.POINTER
+    sig = {
+        "pf_abi_version": (i32, []), "pf_device_count": (i32, []), "pf_last_error": (C.c_char_p, [vp]),
+        "pf_sizeof_real": (sz, [i32]), "pf_required_ghost": (i32, [i32]),
+        "pf_create": (i32, [P(vp), i32, i32, i32, i32]), "pf_create_slab": (i32, [P(vp), i32, i32, i32, i32, P(pf_slab)]),
+        "pf_destroy": (None, [vp]), "pf_reset_state": (i32, [vp]),
+        "pf_field_alloc": (i32, [vp, P(vp)]), "pf_field_free": (i32, [vp, vp]), "pf_field_rows": (i32, [vp, P(i32), P(i32)]),
+        "pf_upload": (i32, [vp, vp, vp, sz, i32]), "pf_download": (i32, [vp, vp, vp, sz, i32]),
+        "pf_step": (i32, [vp, P(pf_params), vp, vp, vp, vp, P(pf_step_info)]),
+        "pf_run": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, P(vp), P(vp), P(i64), P(dbl), P(pf_step_info)]),
+        "pf_step_async": (i32, [vp, P(pf_params), vp, vp, vp, vp]), "pf_sync": (i32, [vp]), "pf_stream": (vp, [vp]),
+        "pf_rhs": (i32, [vp, P(pf_params), i32, P(dbl), P(vp), P(vp), vp, vp]),
+        "pf_cg_solve": (i32, [vp, P(pf_params), i32, vp, vp, vp, vp, dbl, i32, P(i32), P(i32), P(dbl)]),
+        "pf_debug_values": (i32, [vp, P(pf_params), vp, vp, vp, vp, vp]),
+        "pf_stats_delta": (i32, [vp, vp, vp, P(pf_delta_stats)]),
+        "pf_halo_region": (i32, [vp, vp, i32, P(vp), P(vp), P(sz)]),
+        "pf_kernel_launches": (i64, [vp]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    if L.pf_abi_version() != PF_ABI_VERSION:
+        raise ImportError(f"libpfsolver.so ABI {L.pf_abi_version()} != binding {PF_ABI_VERSION}: rebuild")
+    _lib = L
+    return L
+
+
+def np_dtype(dtype):
+    return np.float64 if dtype == PF_F64 else np.float32
+
+
+def pf_dtype_of(a):
+    if a.dtype == np.float64:
+        return PF_F64
+    if a.dtype == np.float32:
+        return PF_F32
+    raise TypeError(a.dtype)
+
+
+class Solver:
+    """One pf_solver handle (one GPU, one grid or slab). Thin: every method is one C-ABI call."""
+
+    def __init__(self, nx, ny, dtype=PF_F64, device=0, slab=None):
+        self._h = C.c_void_p()
+        L = lib()
+        self.nx, self.ny, self.dtype, self.device = nx, ny, dtype, device
+        if slab is None:
+            rc = L.pf_create(C.byref(self._h), device, dtype, nx, ny)
+        else:
+            rc = L.pf_create_slab(C.byref(self._h), device, dtype, nx, ny, C.byref(slab))
+        if rc != PF_OK:
+            self._h = C.c_void_p()
+            raise PfError(rc, L.pf_last_error(None).decode())
+        rows, first = C.c_int(0), C.c_int(0)
+        L.pf_field_rows(self._h, C.byref(rows), C.byref(first))
+        self.rows_alloc, self.first_owned_row = rows.value, first.value
+        self._fields = []
+
+    # -- lifetime
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            for f in list(self._fields):
+                lib().pf_field_free(self._h, f)
+            self._fields.clear()
+            lib().pf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != PF_OK:
+            raise PfError(rc, lib().pf_last_error(self._h).decode())
+
+    # -- fields
+    def field_alloc(self):
+        p = C.c_void_p()
+        self._ck(lib().pf_field_alloc(self._h, C.byref(p)))
+        self._fields.append(p.value)
+        return p.value
+
+    def field_free(self, f):
+        self._ck(lib().pf_field_free(self._h, f))
+        self._fields.remove(f)
+
+    def upload(self, dev, host, offset_elems=0):
+        host = np.ascontiguousarray(host)
+        rs = 8 if self.dtype == PF_F64 else 4
+        self._ck(lib().pf_upload(self._h, dev + offset_elems * rs, host.ctypes.data, host.size, pf_dtype_of(host)))
+
+    def download(self, dev, shape=None, dtype=None, offset_elems=0, out=None):
+        if out is None:
+            shape = shape if shape is not None else (self.rows_alloc, self.nx)
+            out = np.empty(shape, dtype=dtype if dtype is not None else np_dtype(self.dtype))
+        rs = 8 if self.dtype == PF_F64 else 4
+        self._ck(lib().pf_download(self._h, dev + offset_elems * rs, out.ctypes.data, out.size, pf_dtype_of(out)))
+        return out
+
+    def field_from(self, host):
+        f = self.field_alloc()
+        self.upload(f, host)
+        return f
+
+    # -- stepping
+    def step(self, params, F, U, next_F, next_U):
+        info = pf_step_info()
+        self._ck(lib().pf_step(self._h, C.byref(params), F, U, next_F, next_U, C.byref(info)))
+        return info
+
+    def step_async(self, params, F, U, next_F, next_U):
+        self._ck(lib().pf_step_async(self._h, C.byref(params), F, U, next_F, next_U))
+
+    def run(self, params, F, U, F_tmp, U_tmp, n_steps, stop_time=0.0):
+        Fo, Uo, done, t = C.c_void_p(), C.c_void_p(), C.c_int64(0), C.c_double(0)
+        info = pf_step_info()
+        self._ck(lib().pf_run(self._h, C.byref(params), F, U, F_tmp, U_tmp, n_steps, stop_time,
+                              C.byref(Fo), C.byref(Uo), C.byref(done), C.byref(t), C.byref(info)))
+        return Fo.value, Uo.value, done.value, t.value, info
+
+    def sync(self):
+        self._ck(lib().pf_sync(self._h))
+
+    def reset_state(self):
+        self._ck(lib().pf_reset_state(self._h))
+
+    @property
+    def stream(self):
+        return lib().pf_stream(self._h)
+
+    @property
+    def kernel_launches(self):
+        return lib().pf_kernel_launches(self._h)
+
+    # -- building blocks
+    def rhs(self, params, weights, Fs, Us, out_F, out_U):
+        n = len(weights)
+        w = (C.c_double * n)(*[float(x) for x in weights])
+        pf = (C.c_void_p * n)(*Fs)
+        pu = (C.c_void_p * n)(*Us)
+        self._ck(lib().pf_rhs(self._h, C.byref(params), n, w, pf, pu, out_F, out_U))
+
+    def cg_solve(self, params, which, aniso, b, x0, x, tolerance, max_iters):
+        it, conv, err = C.c_int(0), C.c_int(0), C.c_double(0)
+        self._ck(lib().pf_cg_solve(self._h, C.byref(params), which, aniso, b, x0, x, tolerance, max_iters,
+                                   C.byref(it), C.byref(conv), C.byref(err)))
+        return it.value, bool(conv.value), err.value
+
+    def debug_values(self, params, F, U, grad_F, grad_U, aniso):
+        self._ck(lib().pf_debug_values(self._h, C.byref(params), F, U, grad_F, grad_U, aniso))
+
+    def stats_delta(self, a, b):
+        out = pf_delta_stats()
+        self._ck(lib().pf_stats_delta(self._h, a, b, C.byref(out)))
+        return out
+
+    def halo_region(self, field, side):
+        send, recv, n = C.c_void_p(), C.c_void_p(), C.c_size_t(0)
+        self._ck(lib().pf_halo_region(self._h, field, side, C.byref(send), C.byref(recv), C.byref(n)))
+        return send.value, recv.value, n.value
