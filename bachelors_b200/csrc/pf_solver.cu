@@ -48,6 +48,7 @@ struct pf_solver {
     int last_num_steps = 0;                 // simulation.cu:936
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
+    bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
     int64_t launches = 0;
     std::string err;
 
@@ -278,6 +279,24 @@ int pf_download(pf_solver* s, const void* dev, void* host, size_t count, int hos
     return PF_OK;
 }
 
+int pf_upload_raw(pf_solver* s, void* dev, const void* host, size_t bytes)
+{
+    if(int rc = bind(s)) return rc;
+    if(!dev || !host) return fail(s, PF_ERR_INVALID, "pf_upload_raw: NULL pointer");
+    PF_CUDA(s, cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, s->stream));
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
+int pf_download_raw(pf_solver* s, const void* dev, void* host, size_t bytes)
+{
+    if(int rc = bind(s)) return rc;
+    if(!dev || !host) return fail(s, PF_ERR_INVALID, "pf_download_raw: NULL pointer");
+    PF_CUDA(s, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s->stream));
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    return PF_OK;
+}
+
 int pf_sync(pf_solver* s)
 {
     if(int rc = bind(s)) return rc;
@@ -478,85 +497,127 @@ template <> float decode_err<float>(unsigned long long bits) { uint32_t u = (uin
 static inline double pf_pow(double a, double b) { return pow(a, b); }
 static inline float pf_pow(float a, float b) { return powf(a, b); }
 
-// explicit_solver_rk4_adaptive_step (Runge-Kutta-Merson): reference simulation.cu:350-497.
+// explicit_solver_rk4_adaptive_step (Runge-Kutta-Merson): reference simulation.cu:350-497, split into the three
+// phases a multi-rank caller needs (begin / attempt / decide); pf_step runs them back to back.
 // The step-size controller runs on the host in Real arithmetic with the same libm pow as the reference's host code.
+
+// :363-386 - the carried step size and, on the per-stage path, k1 (computed once per step, outside the attempt loop).
 template <typename Real>
-static int rk4_adaptive_step(pf_solver* s, const pf_params& p, const Real* F, const Real* U, Real* nF, Real* nU, pf_step_info* info, double* dt_out)
+static int rkm_begin(pf_solver* s, const pf_params& p, const Real* F, const Real* U, double* tau_out)
 {
     if(s->adaptive_tau <= 0) s->adaptive_tau = (double)(Real) p.dt;        // :363-365
-    Real tau = (Real) s->adaptive_tau;
-    Real epsilon_F = 0, epsilon_U = 0;
-    const bool fused = fused_eligible(s, p);
-    Real* k[10] = {};
-    size_t N = s->field_elems();
-    if(!fused)
+    *tau_out = s->adaptive_tau;
+    s->rkm_fused = fused_eligible(s, p);
+    if(!s->rkm_fused)
     {
         if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "mixed boundary types are single-GPU only");
+        Real* k[10];
         for(int i = 0; i < 10; i++) { void* q; if(int rc = get_scratch(s, i, &q)) return rc; k[i] = (Real*) q; }
         Real w[1] = {1}; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
         if(int rc = launch_rhs_general<Real>(s, p, false, 1, w, Fs, Us, k[0], k[5])) return rc;      // k1, :386
     }
-    bool converged = false;
-    int i = 0;
-    int max_iters = std::max(std::max(p.T_max_iters, p.Phi_max_iters), 1);  // :390
-    Real used_tau = tau;
+    return PF_OK;
+}
+
+// :406-435 - k2..k5 for the step size tau and the two max-norms, left on the device in s->d_err (as bit patterns).
+// On the fused path the kernel also writes the candidate result y + tau/6 (k1 + 4 k4 + k5) into nF/nU (:471-476).
+template <typename Real>
+static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
+{
+    const Real tau = (Real) tau_d;
+    PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
+    if(s->rkm_fused)
+    {
+        FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+        a.w[0] = tau / 3; a.w[1] = tau / 6; a.w[2] = tau / 8; a.w[3] = tau * 3 / 8;
+        a.w[4] = tau / 2; a.w[5] = -tau * 3 / 2; a.w[6] = tau * 2; a.w[7] = tau / 6;
+        return launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a);
+    }
+    Real* k[10];
+    for(int i = 0; i < 10; i++) k[i] = (Real*) s->scratch[i];
+    Real *k1F = k[0], *k2F = k[1], *k3F = k[2], *k4F = k[3], *k5F = k[4], *k1U = k[5], *k2U = k[6], *k3U = k[7], *k4U = k[8], *k5U = k[9];
+    { Real w[2] = {1, tau / 3}; const Real* Fs[2] = {F, k1F}; const Real* Us[2] = {U, k1U};
+      if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k2F, k2U)) return rc; }
+    { Real w[3] = {1, tau / 6, tau / 6}; const Real* Fs[3] = {F, k1F, k2F}; const Real* Us[3] = {U, k1U, k2U};
+      if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k3F, k3U)) return rc; }
+    { Real w[3] = {1, tau / 8, tau * 3 / 8}; const Real* Fs[3] = {F, k1F, k3F}; const Real* Us[3] = {U, k1U, k3U};
+      if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k4F, k4U)) return rc; }
+    { Real w[4] = {1, tau / 2, -tau * 3 / 2, tau * 2}; const Real* Fs[4] = {F, k1F, k3F, k4F}; const Real* Us[4] = {U, k1U, k3U, k4U};
+      if(int rc = launch_rhs_general<Real>(s, p, false, 4, w, Fs, Us, k5F, k5U)) return rc; }
+    const size_t N = s->field_elems();
+    const int blocks = elementwise_blocks(s, N, 256);
+    k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1F, k3F, k4F, k5F, s->d_err + 0); PF_LAUNCH_CHECK(s);
+    k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1U, k3U, k4U, k5U, s->d_err + 1); PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+// :437-467 - the accept test and the step-size controller, from the (globally reduced) max-norm bit patterns.
+// *stop: 0 = try again with *next_tau, 1 = accepted, 2 = the min_dt floor was reached (the reference `break`s there,
+// accepted or not, without counting the attempt).
+template <typename Real>
+static void rkm_decide(const pf_params& p, double tau_d, unsigned long long bits_F, unsigned long long bits_U,
+                       int* converged, int* stop, double* next_tau, double* eps_F, double* eps_U)
+{
+    const Real tau = (Real) tau_d;
+    const Real max_F = decode_err<Real>(bits_F);
+    const Real max_U = decode_err<Real>(bits_U);
+    const Real epsilon_F = tau / 3 * max_F;                                 // :437-438
+    const Real epsilon_U = tau / 3 * max_U;
+    *converged = ((double) epsilon_F < p.Phi_tolerance && (double) epsilon_U < p.T_tolerance) ? 1 : 0;   // :456
+    const double e_max = (double)(epsilon_F > epsilon_U ? epsilon_F : epsilon_U);
+    const Real epsilon = (Real)(e_max > 1e-20 ? e_max : 1e-20);             // :459
+    const double d_min = p.Phi_tolerance < p.T_tolerance ? p.Phi_tolerance : p.T_tolerance;
+    const Real delta = (Real)(d_min > 1e-20 ? d_min : 1e-20);               // :460
+    Real nt = pf_pow(delta / epsilon, (Real) 0.2) * 4 / 5 * tau;            // :462
+    nt = (Real)((double) nt > p.min_dt ? (double) nt : p.min_dt);           // :463
+    const bool floor_hit = (double) nt <= p.min_dt && (double) tau <= p.min_dt;   // :466
+    *stop = floor_hit ? 2 : (*converged ? 1 : 0);
+    *next_tau = (double) nt;
+    *eps_F = (double) epsilon_F; *eps_U = (double) epsilon_U;
+}
+
+// :471-476 on the per-stage path (the fused kernel has already written the result).
+template <typename Real>
+static int rkm_finish(pf_solver* s, double used_tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
+{
+    if(s->rkm_fused) return PF_OK;
+    const Real used_tau = (Real) used_tau_d;
+    Real* k[10];
+    for(int i = 0; i < 10; i++) k[i] = (Real*) s->scratch[i];
+    const size_t N = s->field_elems();
+    const int blocks = elementwise_blocks(s, N, 256);
+    k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, F, k[0], k[3], k[4], nF); PF_LAUNCH_CHECK(s);
+    k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, U, k[5], k[8], k[9], nU); PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+template <typename Real>
+static int rk4_adaptive_step(pf_solver* s, const pf_params& p, const Real* F, const Real* U, Real* nF, Real* nU, pf_step_info* info, double* dt_out)
+{
+    double tau = 0;
+    if(int rc = rkm_begin<Real>(s, p, F, U, &tau)) return rc;
+    const int max_iters = std::max(std::max(p.T_max_iters, p.Phi_max_iters), 1);  // :390
+    int converged = 0, stop = 0, i = 0;
+    double used_tau = tau, eps_F = 0, eps_U = 0;
     for(; i < max_iters && !converged; i++)
     {
-        PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
-        if(fused)
-        {
-            FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
-            a.w[0] = tau / 3; a.w[1] = tau / 6; a.w[2] = tau / 8; a.w[3] = tau * 3 / 8;
-            a.w[4] = tau / 2; a.w[5] = -tau * 3 / 2; a.w[6] = tau * 2; a.w[7] = tau / 6;
-            if(int rc = launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a)) return rc;
-        }
-        else
-        {
-            Real *k1F = k[0], *k2F = k[1], *k3F = k[2], *k4F = k[3], *k5F = k[4], *k1U = k[5], *k2U = k[6], *k3U = k[7], *k4U = k[8], *k5U = k[9];
-            { Real w[2] = {1, tau / 3}; const Real* Fs[2] = {F, k1F}; const Real* Us[2] = {U, k1U};
-              if(int rc = launch_rhs_general<Real>(s, p, false, 2, w, Fs, Us, k2F, k2U)) return rc; }
-            { Real w[3] = {1, tau / 6, tau / 6}; const Real* Fs[3] = {F, k1F, k2F}; const Real* Us[3] = {U, k1U, k2U};
-              if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k3F, k3U)) return rc; }
-            { Real w[3] = {1, tau / 8, tau * 3 / 8}; const Real* Fs[3] = {F, k1F, k3F}; const Real* Us[3] = {U, k1U, k3U};
-              if(int rc = launch_rhs_general<Real>(s, p, false, 3, w, Fs, Us, k4F, k4U)) return rc; }
-            { Real w[4] = {1, tau / 2, -tau * 3 / 2, tau * 2}; const Real* Fs[4] = {F, k1F, k3F, k4F}; const Real* Us[4] = {U, k1U, k3U, k4U};
-              if(int rc = launch_rhs_general<Real>(s, p, false, 4, w, Fs, Us, k5F, k5U)) return rc; }
-            int blocks = elementwise_blocks(s, N, 256);
-            k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1F, k3F, k4F, k5F, s->d_err + 0); PF_LAUNCH_CHECK(s);
-            k_rkm_error<Real><<<blocks, 256, 0, s->stream>>>(N, k1U, k3U, k4U, k5U, s->d_err + 1); PF_LAUNCH_CHECK(s);
-        }
+        if(int rc = rkm_attempt<Real>(s, p, tau, F, U, nF, nU)) return rc;
         PF_CUDA(s, cudaMemcpyAsync(s->h_err, s->d_err, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
         PF_CUDA(s, cudaStreamSynchronize(s->stream));
-        Real max_F = decode_err<Real>(s->h_err[0]);
-        Real max_U = decode_err<Real>(s->h_err[1]);
-        epsilon_F = tau / 3 * max_F;                                        // :437-438
-        epsilon_U = tau / 3 * max_U;
-
-        if((double) epsilon_F < p.Phi_tolerance && (double) epsilon_U < p.T_tolerance) converged = true;   // :456
-        double e_max = (double)(epsilon_F > epsilon_U ? epsilon_F : epsilon_U);
-        Real epsilon = (Real)(e_max > 1e-20 ? e_max : 1e-20);               // :459
-        double d_min = p.Phi_tolerance < p.T_tolerance ? p.Phi_tolerance : p.T_tolerance;
-        Real delta = (Real)(d_min > 1e-20 ? d_min : 1e-20);                 // :460
         used_tau = tau;
-        tau = pf_pow(delta / epsilon, (Real) 0.2) * 4 / 5 * tau;            // :462
-        tau = (Real)((double) tau > p.min_dt ? (double) tau : p.min_dt);    // :463
-        if((double) tau <= p.min_dt && (double) used_tau <= p.min_dt) break;   // :466
+        rkm_decide<Real>(p, used_tau, s->h_err[0], s->h_err[1], &converged, &stop, &tau, &eps_F, &eps_U);
+        if(stop == 2) break;                                                // :466: `break` skips the loop's i++
     }
-    if(!fused)
-    {
-        int blocks = elementwise_blocks(s, N, 256);
-        k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, F, k[0], k[3], k[4], nF); PF_LAUNCH_CHECK(s);
-        k_rkm_combine<Real><<<blocks, 256, 0, s->stream>>>(N, used_tau / 6, U, k[5], k[8], k[9], nU); PF_LAUNCH_CHECK(s);
-    }
-    s->adaptive_tau = (double) tau;                                         // :486
+    if(int rc = rkm_finish<Real>(s, used_tau, F, U, nF, nU)) return rc;
+    s->adaptive_tau = tau;                                                  // :486
     if(info)
     {
-        info->Phi_iters = i; info->T_iters = i;
+        info->Phi_iters = i; info->T_iters = i;                             // :488-492
         info->Phi_converged = converged; info->T_converged = converged;
-        info->Phi_error = (double) epsilon_F; info->T_error = (double) epsilon_U;
-        info->next_tau = (double) tau;
+        info->Phi_error = eps_F; info->T_error = eps_U;
+        info->next_tau = tau;
     }
-    *dt_out = (double) used_tau;
+    *dt_out = used_tau;
     return PF_OK;
 }
 
@@ -818,6 +879,48 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
     if(U_out) *U_out = cU;
     if(steps_done) *steps_done = i;
     if(t_advanced) *t_advanced = t - params->time;
+    return PF_OK;
+}
+
+int pf_rkm_begin(pf_solver* s, const pf_params* params, const void* F, const void* U, double* tau)
+{
+    if(int rc = bind(s)) return rc;
+    if(!params || !F || !U || !tau) return fail(s, PF_ERR_INVALID, "pf_rkm_begin: NULL argument");
+    if(params->nx != s->nx || params->ny != s->ny) return fail(s, PF_ERR_INVALID, "pf_rkm_begin: size mismatch");
+    return s->dtype == PF_F64 ? rkm_begin<double>(s, *params, (const double*) F, (const double*) U, tau)
+                              : rkm_begin<float>(s, *params, (const float*) F, (const float*) U, tau);
+}
+
+int pf_rkm_attempt_async(pf_solver* s, const pf_params* params, double tau, const void* F, const void* U, void* next_F, void* next_U)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    return s->dtype == PF_F64 ? rkm_attempt<double>(s, *params, tau, (const double*) F, (const double*) U, (double*) next_F, (double*) next_U)
+                              : rkm_attempt<float>(s, *params, tau, (const float*) F, (const float*) U, (float*) next_F, (float*) next_U);
+}
+
+void* pf_rkm_error_bits(pf_solver* s) { return s ? (void*) s->d_err : nullptr; }
+
+int pf_rkm_decide(pf_solver* s, const pf_params* params, double tau, uint64_t bits_Phi, uint64_t bits_T,
+                  int* converged, int* stop, double* next_tau, double* eps_Phi, double* eps_T)
+{
+    if(!s || !params || !converged || !stop || !next_tau) return fail(s, PF_ERR_INVALID, "pf_rkm_decide: NULL argument");
+    double eF = 0, eU = 0;
+    if(s->dtype == PF_F64) rkm_decide<double>(*params, tau, bits_Phi, bits_T, converged, stop, next_tau, &eF, &eU);
+    else                   rkm_decide<float>(*params, tau, bits_Phi, bits_T, converged, stop, next_tau, &eF, &eU);
+    if(eps_Phi) *eps_Phi = eF;
+    if(eps_T) *eps_T = eU;
+    return PF_OK;
+}
+
+int pf_rkm_finish_async(pf_solver* s, const pf_params* params, double used_tau, double next_tau, const void* F, const void* U, void* next_F, void* next_U)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    int rc = s->dtype == PF_F64 ? rkm_finish<double>(s, used_tau, (const double*) F, (const double*) U, (double*) next_F, (double*) next_U)
+                                : rkm_finish<float>(s, used_tau, (const float*) F, (const float*) U, (float*) next_F, (float*) next_U);
+    if(rc) return rc;
+    s->adaptive_tau = next_tau;                                             // simulation.cu:486
     return PF_OK;
 }
 

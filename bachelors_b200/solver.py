@@ -16,7 +16,8 @@ LIB_PATH = os.path.join(_HERE, "libpfsolver.so")
 EXPORTS = [
     "pf_abi_version", "pf_device_count", "pf_last_error", "pf_sizeof_real", "pf_required_ghost",
     "pf_create", "pf_create_slab", "pf_destroy", "pf_reset_state",
-    "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download",
+    "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download", "pf_upload_raw", "pf_download_raw",
+    "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
     "pf_step", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
 ]
@@ -49,6 +50,12 @@ def lib():
         "pf_destroy": (None, [vp]), "pf_reset_state": (i32, [vp]),
         "pf_field_alloc": (i32, [vp, P(vp)]), "pf_field_free": (i32, [vp, vp]), "pf_field_rows": (i32, [vp, P(i32), P(i32)]),
         "pf_upload": (i32, [vp, vp, vp, sz, i32]), "pf_download": (i32, [vp, vp, vp, sz, i32]),
+        "pf_upload_raw": (i32, [vp, vp, vp, sz]), "pf_download_raw": (i32, [vp, vp, vp, sz]),
+        "pf_rkm_begin": (i32, [vp, P(pf_params), vp, vp, P(dbl)]),
+        "pf_rkm_attempt_async": (i32, [vp, P(pf_params), dbl, vp, vp, vp, vp]),
+        "pf_rkm_error_bits": (vp, [vp]),
+        "pf_rkm_decide": (i32, [vp, P(pf_params), dbl, C.c_uint64, C.c_uint64, P(i32), P(i32), P(dbl), P(dbl), P(dbl)]),
+        "pf_rkm_finish_async": (i32, [vp, P(pf_params), dbl, dbl, vp, vp, vp, vp]),
         "pf_step": (i32, [vp, P(pf_params), vp, vp, vp, vp, P(pf_step_info)]),
         "pf_run": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, P(vp), P(vp), P(i64), P(dbl), P(pf_step_info)]),
         "pf_step_async": (i32, [vp, P(pf_params), vp, vp, vp, vp]), "pf_sync": (i32, [vp]), "pf_stream": (vp, [vp]),

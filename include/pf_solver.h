@@ -159,6 +159,9 @@ PF_API int  pf_field_rows(const pf_solver* s, int* rows_alloc, int* first_owned_
  * then runs on the device exactly like sim_modify_T's staging path. Blocking, like the reference. */
 PF_API int  pf_upload(pf_solver* s, void* dev, const void* host, size_t count, int host_dtype);
 PF_API int  pf_download(pf_solver* s, const void* dev, void* host, size_t count, int host_dtype);
+/* Raw byte copies on the solver's stream, blocking: sim_modify (simulation.cu:1051-1059). */
+PF_API int  pf_upload_raw(pf_solver* s, void* dev, const void* host, size_t bytes);
+PF_API int  pf_download_raw(pf_solver* s, const void* dev, void* host, size_t bytes);
 
 /* ---- the step: replaces sim_step (simulation.cu:1091-1156) ---------------------------------- */
 /* Advances (F, U) by one step of params->solver into (next_F, next_U); all four are device fields of
@@ -182,6 +185,23 @@ PF_API int  pf_step_async(pf_solver* s, const pf_params* params,
                           const void* F, const void* U, void* next_F, void* next_U);
 PF_API int  pf_sync(pf_solver* s);
 PF_API void* pf_stream(pf_solver* s);                        /* cudaStream_t of the solver, for callers that order their own work */
+
+/* ---- the adaptive step in phases, for callers that own a cross-rank reduction ----
+ * explicit_solver_rk4_adaptive_step (simulation.cu:350-497) = begin; { attempt; [all-reduce MAX]; decide } until stop; finish.
+ * pf_step runs exactly this sequence for one rank. A multi-rank caller runs it in lock step on every rank and
+ * max-reduces the two 64-bit words at pf_rkm_error_bits() across ranks between attempt and decide: they are the bit
+ * patterns of the non-negative max-norms, which order like unsigned integers, so an integer MAX all-reduce is exact
+ * and order-independent and every rank takes the identical accept / step-size decision.
+ * pf_rkm_decide: *stop = 0 try again with *next_tau (at most max(T_max_iters, Phi_max_iters, 1) attempts, :390),
+ * 1 = accepted, 2 = min_dt floor reached (:466; the attempt is then not counted in Phi_iters/T_iters). */
+PF_API int   pf_rkm_begin(pf_solver* s, const pf_params* params, const void* F, const void* U, double* tau);
+PF_API int   pf_rkm_attempt_async(pf_solver* s, const pf_params* params, double tau,
+                                  const void* F, const void* U, void* next_F, void* next_U);
+PF_API void* pf_rkm_error_bits(pf_solver* s);                /* device uint64_t[2]: {max|e_Phi|, max|e_T|} of the last attempt */
+PF_API int   pf_rkm_decide(pf_solver* s, const pf_params* params, double tau, uint64_t bits_Phi, uint64_t bits_T,
+                           int* converged, int* stop, double* next_tau, double* eps_Phi, double* eps_T);
+PF_API int   pf_rkm_finish_async(pf_solver* s, const pf_params* params, double used_tau, double next_tau,
+                                 const void* F, const void* U, void* next_F, void* next_U);
 
 /* ---- single building blocks, exported for parity tests and for the viewer ------------------- */
 /* out = f(sum_i w_i * (F_i, U_i)): the RHS of simulation.cu:145-243 with IS_EULER=false, n_states in 1..4. */

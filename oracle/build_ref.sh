@@ -27,7 +27,7 @@ build_sim () { # $1 = suffix, $2.. = extra defines
   if [ ! "$OUT/simulation_$sfx.o" -nt "$REF/simulation.cu" ]; then
     (cd "$REF" && $NVCC $ARCH $DEV_FLAGS "$@" -c simulation.cu -o "$OUT/simulation_$sfx.o")
   fi
-  $NVCC $ARCH -std=c++17 -O2 -Xcompiler -fPIC -w "$@" -Xcompiler -iquote -Xcompiler "$REF" \
+  $NVCC $ARCH -std=c++17 -O2 -Xcompiler -fPIC -w "$@" -Xcompiler -iquote -Xcompiler "$REF" -I"$HERE/../include" \
       -c "$HERE/ref_glue/ref_glue.cpp" -o "$OUT/ref_glue_$sfx.o"
   $NVCC $ARCH -shared -o "$OUT/libref_sim_$sfx.so" "$OUT/simulation_$sfx.o" "$OUT/ref_glue_$sfx.o" -lcudart
   rm -f "$OUT/ref_glue_$sfx.o"

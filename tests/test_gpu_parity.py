@@ -1,0 +1,427 @@
+"""Parity of the CUDA path (through the C-ABI, bachelors_b200/libpfsolver.so) with the CPU oracle, with the golden
+outputs of the reference, and - when oracle/_ref was built - with the UNMODIFIED reference running on the same GPU.
+
+Bars (BASELINE.json north_star): rel-L2 <= 1e-10 (fp64) / 1e-5 (fp32), CG iteration counts +-1, bit-stable runs.
+The explicit solvers are held to the stronger bar of bit-identity with the oracle.
+"""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from bachelors_b200 import solver as S
+from bachelors_b200._abi import (PF_ERR_INVALID, PF_ERR_UNSUPPORTED, PF_F32, PF_F64, default_params, pf_slab)
+from bachelors_b200.config import read_config
+from bachelors_b200.initial import make_initial_conditions
+from bachelors_b200.testing import seeded_fields
+from conftest import GOLDEN, ROOT
+from golden_cases import all_cases, case_inputs
+from oracle import ref_sim
+from oracle.oracle import Oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_l2(a, b):
+    a = a.astype(np.float64); b = b.astype(np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def tol_of(dtype):
+    return 1e-10 if dtype == PF_F64 else 1e-5
+
+
+def cuda_replay(case_or_params, F0=None, U0=None, dtype=None, steps=None):
+    if isinstance(case_or_params, dict):
+        p, F0, U0, dtype = case_inputs(case_or_params)
+        steps = case_or_params["steps"]
+    else:
+        p = case_or_params
+    with S.Solver(p.nx, p.ny, dtype) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        t = 0.0
+        infos = []
+        q = p.copy()
+        for i in range(steps):
+            q.iter = i; q.time = t
+            info = s.step(q, F, U, nF, nU)
+            t += info.dt_advanced
+            infos.append((info.dt_advanced, info.Phi_iters, info.T_iters, info.Phi_converged, info.T_converged, info.Phi_error, info.T_error))
+            F, nF = nF, F; U, nU = nU, U
+        return s.download(F), s.download(U), t, np.array(infos, dtype=np.float64)
+
+
+def oracle_replay(p, F0, U0, dtype, steps):
+    o = Oracle(dtype, p.nx, p.ny)
+    F, U, t, infos = F0, U0, 0.0, []
+    q = p.copy()
+    for i in range(steps):
+        q.iter = i; q.time = t
+        F, U, dt, info = o.step(q, F, U)
+        t += dt
+        infos.append((dt, info.Phi_iters, info.T_iters, info.Phi_converged, info.T_converged, info.Phi_error, info.T_error))
+    return F, U, t, np.array(infos, dtype=np.float64)
+
+
+def check_against(case, got, want, want_name):
+    F, U, t, infos = got
+    wF, wU, wt, winfos = want
+    dtype = PF_F64 if case["dtype"] == "f64" else PF_F32
+    eF, eU = rel_l2(F, wF), rel_l2(U, wU)
+    assert eF <= tol_of(dtype) and eU <= tol_of(dtype), (want_name, eF, eU)
+    assert abs(t - wt) <= (1e-12 if dtype == PF_F64 else 1e-6) * max(abs(wt), 1e-30), (want_name, t, wt)
+    if case["solver"] == "semi-implicit":
+        assert np.all(np.abs(infos[:, 1:3] - winfos[:, 1:3]) <= 1), (want_name, infos[:, 1:3], winfos[:, 1:3])
+    if case["solver"] == "explicit-rk4-adaptive":
+        assert np.array_equal(infos[:, 1], winfos[:, 1]), (want_name, infos[:, 1], winfos[:, 1])
+    return eF, eU
+
+
+# ---- the golden cases: CUDA vs oracle, vs the reference's stored outputs ---------------------------------------------
+@pytest.mark.parametrize("case", all_cases(), ids=lambda c: c["name"])
+def test_cuda_matches_oracle_and_golden(case):
+    got = cuda_replay(case)
+    p, F0, U0, dtype = case_inputs(case)
+    want = oracle_replay(p, F0, U0, dtype, case["steps"])
+    check_against(case, got, want, "oracle")
+    if case["solver"] != "semi-implicit":
+        # same arithmetic, same order: bit-identical (reductions in the explicit solvers are max-norms, order-free)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), "not bit-identical to the oracle"
+        assert np.array_equal(got[3][:, 0], want[3][:, 0])
+    path = os.path.join(GOLDEN, case["name"] + ".npz")
+    assert os.path.exists(path), f"{path} missing"
+    g = np.load(path)
+    check_against(case, got, (g["F"], g["U"], float(g["t"]), g["step_info"]), "golden(reference on B200)")
+
+
+LIVE = [c for c in all_cases() if c["name"].split("_f")[0] in
+        ("euler_neumann", "euler_dirichlet_aniso", "rk4_neumann_aniso_noise", "rk4_periodic", "rkm_neumann", "si_neumann", "si_theta_half_guess")]
+
+
+@pytest.mark.parametrize("case", LIVE, ids=lambda c: c["name"])
+def test_cuda_matches_live_reference(case):
+    """The unmodified reference (oracle A) on the same GPU, longer runs than the golden fixtures."""
+    p, F0, U0, dtype = case_inputs(case)
+    if not ref_sim.available(dtype):
+        pytest.skip("oracle/_ref not built")
+    steps = case["steps"] * 5
+    with ref_sim.RefSim(dtype, p.nx, p.ny, fresh=True) as ref:
+        ref.upload(F0, U0)
+        infos, t = [], 0.0
+        q = p.copy()
+        for i in range(steps):
+            q.iter = i; q.time = t
+            dt, info = ref.run(q, 1)
+            t += dt
+            infos.append((dt, info.Phi_iters, info.T_iters, info.Phi_converged, info.T_converged, info.Phi_error, info.T_error))
+        rF, rU = ref.download()
+    got = cuda_replay(p, F0, U0, dtype, steps)
+    eF, eU = check_against(case, got, (rF, rU, t, np.array(infos)), "live reference")
+    if case["solver"] in ("explicit", "explicit-rk4"):
+        assert eF == 0 and eU == 0, (eF, eU)
+
+
+# ---- ragged / degenerate sizes against the oracle ---------------------------------------------------------------------
+SIZES = [(1, 1), (1, 7), (5, 1), (2, 3), (63, 5), (65, 33), (129, 31), (57, 97), (257, 66)]
+
+
+@pytest.mark.parametrize("bc", ["neumann", "dirichlet", "periodic"])
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive"])
+def test_ragged_sizes_bit_identical(solver, bc):
+    for dtype, npdt in ((PF_F64, np.float64), (PF_F32, np.float32)):
+        for nx, ny in SIZES:
+            tolv = 5e-9 if dtype == PF_F64 else 5e-5
+            p = default_params(solver=solver, nx=nx, ny=ny, L0=max(nx, ny) / 128.0, S=0.25, Phi_boundary=bc, T_boundary=bc,
+                               Phi_tolerance=tolv, T_tolerance=tolv)
+            F0, U0 = seeded_fields(nx, ny, npdt, kind="noise", seed=nx * 1000 + ny)
+            got = cuda_replay(p, F0, U0, dtype, 2)
+            want = oracle_replay(p, F0, U0, dtype, 2)
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (nx, ny, dtype, rel_l2(got[0], want[0]))
+            assert np.array_equal(got[3][:, :3], want[3][:, :3])
+
+
+@pytest.mark.parametrize("bc", ["neumann", "dirichlet", "periodic"])
+def test_semi_implicit_ragged_sizes(bc):
+    for dtype, npdt in ((PF_F64, np.float64), (PF_F32, np.float32)):
+        for nx, ny in [(1, 1), (3, 5), (65, 33), (300, 7), (257, 66)]:
+            tolv = 5e-9 if dtype == PF_F64 else 1e-5
+            p = default_params(solver="semi-implicit", nx=nx, ny=ny, L0=max(nx, ny) / 128.0, S=0.25, Phi_boundary=bc, T_boundary=bc,
+                               Phi_tolerance=tolv, T_tolerance=tolv)
+            F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+            got = cuda_replay(p, F0, U0, dtype, 2)
+            want = oracle_replay(p, F0, U0, dtype, 2)
+            assert rel_l2(got[0], want[0]) <= tol_of(dtype) and rel_l2(got[1], want[1]) <= tol_of(dtype), (nx, ny, dtype)
+            assert np.all(np.abs(got[3][:, 1:3] - want[3][:, 1:3]) <= 1), (nx, ny, got[3][:, 1:3], want[3][:, 1:3])
+
+
+# ---- building blocks ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32])
+def test_rhs_blends_match_oracle(dtype):
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    nx, ny = 70, 45
+    rng = np.random.default_rng(5)
+    for Fb, Ub in (("neumann", "neumann"), ("periodic", "dirichlet"), ("dirichlet", "periodic")):
+        p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=nx / 128.0, S=0.3, Phi_boundary=Fb, T_boundary=Ub)
+        fields = [seeded_fields(nx, ny, npdt, kind="noise", seed=i + 1) for i in range(4)]
+        for n in (1, 2, 3, 4):
+            w = [1.0] + list(rng.uniform(-1e-5, 1e-5, n - 1))
+            o = Oracle(dtype, nx, ny)
+            wF, wU = o.rhs(p, w, [f[0] for f in fields[:n]], [f[1] for f in fields[:n]])
+            with S.Solver(nx, ny, dtype) as s:
+                Fs = [s.field_from(f[0]) for f in fields[:n]]
+                Us = [s.field_from(f[1]) for f in fields[:n]]
+                oF, oU = s.field_alloc(), s.field_alloc()
+                s.rhs(p, w, Fs, Us, oF, oU)
+                gF, gU = s.download(oF), s.download(oU)
+            assert np.array_equal(gF, wF) and np.array_equal(gU, wU), (Fb, Ub, n)
+
+
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32])
+def test_cg_solve_matches_oracle(dtype):
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    nx, ny = 96, 80
+    for bc in ("neumann", "dirichlet", "periodic"):
+        p = default_params(solver="semi-implicit", nx=nx, ny=ny, L0=nx / 128.0, Phi_boundary=bc, T_boundary=bc, dt=2e-5)
+        rng = np.random.default_rng(11)
+        factor = rng.uniform(0.2, 0.5, (ny, nx)).astype(npdt)
+        b, x0 = seeded_fields(nx, ny, npdt, kind="smooth")
+        for which in (0, 1):
+            for use_x0 in (True, False):
+                tolv = 1e-9 if dtype == PF_F64 else 1e-5
+                o = Oracle(dtype, nx, ny)
+                wx, wit, wconv, werr = o.cg_solve(p, which, factor if which == 0 else None, b, x0 if use_x0 else None, tolv, 50)
+                with S.Solver(nx, ny, dtype) as s:
+                    db, dx0, dfac, dx = s.field_from(b), s.field_from(x0), s.field_from(factor), s.field_alloc()
+                    it, conv, err = s.cg_solve(p, which, dfac if which == 0 else None, db, dx0 if use_x0 else None, dx, tolv, 50)
+                    gx = s.download(dx)
+                assert abs(it - wit) <= 1 and conv == wconv, (bc, which, use_x0, it, wit)
+                assert rel_l2(gx, wx) <= tol_of(dtype)
+                assert wit >= 1 and np.isfinite(err)
+
+
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32])
+def test_debug_values_and_stats(dtype):
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    nx, ny = 77, 51
+    p = default_params(nx=nx, ny=ny, L0=nx / 128.0, S=0.3, Phi_boundary="periodic", T_boundary="neumann")
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    o = Oracle(dtype, nx, ny)
+    wg, wh, wa = o.debug_values(p, F0, U0)
+    ws = o.stats_delta(F0, U0)
+    with S.Solver(nx, ny, dtype) as s:
+        F, U = s.field_from(F0), s.field_from(U0)
+        g, h, a = s.field_alloc(), s.field_alloc(), s.field_alloc()
+        s.debug_values(p, F, U, g, h, a)
+        assert np.array_equal(s.download(g), wg) and np.array_equal(s.download(h), wh) and np.array_equal(s.download(a), wa)
+        st = s.stats_delta(F, U)
+    rt = 1e-12 if dtype == PF_F64 else 1e-4
+    assert st.min == ws.min and st.max == ws.max
+    assert abs(st.L1 - ws.L1) <= rt * abs(ws.L1) and abs(st.L2 - ws.L2) <= rt * abs(ws.L2) and abs(st.sum - ws.sum) <= rt * abs(ws.L1)
+
+
+def test_step_stats_and_residuals_match_oracle():
+    nx, ny = 64, 48
+    p = default_params(solver="explicit", nx=nx, ny=ny, L0=nx / 128.0, do_stats=1, do_stats_step_residual=1, do_corrector_loop=1, corrector_max_iters=2)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    o = Oracle(PF_F64, nx, ny)
+    wF, wU, _, winfo = o.step(p, F0, U0)
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        info = s.step(p, F, U, nF, nU)
+        assert np.array_equal(s.download(nF), wF) and np.array_equal(s.download(nU), wU)
+    assert info.step_res_count == winfo.step_res_count == 2
+    for a, b in ((info.Phi_delta, winfo.Phi_delta), (info.T_delta, winfo.T_delta), (info.step_res[0], winfo.step_res[0]), (info.step_res[1], winfo.step_res[1])):
+        assert a.min == b.min and a.max == b.max and abs(a.L2 - b.L2) <= 1e-12 * max(abs(b.L2), 1e-300) and abs(a.L1 - b.L1) <= 1e-12 * max(abs(b.L1), 1e-300)
+
+
+def test_upload_download_convert():
+    nx, ny = 50, 30
+    a64, _ = seeded_fields(nx, ny, np.float64, kind="noise")
+    with S.Solver(nx, ny, PF_F32) as s:
+        f = s.field_from(a64)                               # double host -> float device (sim_modify_double on a USE_FLOATS build)
+        assert np.array_equal(s.download(f), a64.astype(np.float32))
+        assert np.array_equal(s.download(f, dtype=np.float64), a64.astype(np.float32).astype(np.float64))
+    with S.Solver(nx, ny, PF_F64) as s:
+        f = s.field_from(a64.astype(np.float32))            # float host -> double device (sim_modify_float)
+        assert np.array_equal(s.download(f), a64.astype(np.float32).astype(np.float64))
+        assert np.array_equal(s.download(f, dtype=np.float32), a64.astype(np.float32))
+        z = s.field_alloc()
+        assert not s.download(z).any()                      # REALLOC_ZERO
+
+
+# ---- stepping entry points ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive", "semi-implicit"])
+def test_run_equals_repeated_steps_and_is_bit_stable(solver):
+    nx, ny = 200, 136
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    ref = cuda_replay(p, F0, U0, PF_F64, 7)
+    digests = set()
+    for _ in range(3):
+        with S.Solver(nx, ny, PF_F64) as s:
+            F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+            Fo, Uo, done, t, info = s.run(p, F, U, tF, tU, 7)
+            gF, gU = s.download(Fo), s.download(Uo)
+        assert done == 7 and abs(t - ref[2]) <= 1e-15
+        assert np.array_equal(gF, ref[0]) and np.array_equal(gU, ref[1])
+        digests.add(hashlib.sha256(gF.tobytes() + gU.tobytes()).hexdigest())
+    assert len(digests) == 1
+
+
+def test_run_stops_at_stop_time():
+    nx = ny = 64
+    p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=0.5)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        Fo, Uo, done, t, _ = s.run(p, F, U, tF, tU, 1000, stop_time=10.5 * p.dt)
+        assert done == 11 and Fo == tF
+
+
+def test_async_steps_then_sync():
+    nx, ny = 96, 96
+    p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=nx / 128.0)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    want = cuda_replay(p, F0, U0, PF_F64, 4)
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        for _ in range(4):
+            s.step_async(p, F, U, nF, nU)
+            F, nF = nF, F; U, nU = nU, U
+        s.sync()
+        assert np.array_equal(s.download(F), want[0])
+        assert s.kernel_launches == 4                        # one fused kernel per RK4 step
+
+
+def test_errors_are_returned_not_fatal():
+    with S.Solver(32, 32, PF_F64) as s:
+        F, U, nF, nU = (s.field_alloc() for _ in range(4))
+        with pytest.raises(S.PfError) as e:
+            s.step(default_params(nx=64, ny=32), F, U, nF, nU)           # reference: "Bad sizes provided", simulation.cu:1094
+        assert e.value.code == PF_ERR_INVALID
+        with pytest.raises(S.PfError) as e:
+            s.step(default_params(nx=32, ny=32, solver="exact"), F, U, nF, nU)
+        assert e.value.code == PF_ERR_UNSUPPORTED
+        with pytest.raises(S.PfError) as e:
+            s.step(default_params(nx=32, ny=32), F, U, F, nU)
+        assert e.value.code == PF_ERR_INVALID
+        s.step(default_params(nx=32, ny=32), F, U, nF, nU)               # the handle stays usable
+
+
+# ---- slabs (the multi-GPU decomposition), emulated on one device --------------------------------------------------------
+@pytest.mark.parametrize("bc", ["neumann", "periodic", "dirichlet"])
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive"])
+def test_slabs_reproduce_the_single_grid_bit_for_bit(solver, bc):
+    from bachelors_b200.slabs import slab_layout
+    nx, ny, G, steps = 150, 131, 3, 3
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_boundary=bc, T_boundary=bc, Phi_tolerance=1e-7, T_tolerance=1e-7)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    want = cuda_replay(p, F0, U0, PF_F64, steps)
+    L = S.lib()
+    ghost = L.pf_required_ghost(p.solver)
+    slabs = [slab_layout(ny, G, g, ghost, periodic=(bc == "periodic")) for g in range(G)]
+    solvers = [S.Solver(nx, ny, PF_F64, slab=sl) for sl in slabs]
+    try:
+        def padded(a, sl, s):
+            rows = (np.arange(s.rows_alloc) - s.first_owned_row + sl.y0) % ny
+            return a[rows]
+        st = []
+        for sl, s in zip(slabs, solvers):
+            st.append([s.field_from(padded(F0, sl, s)), s.field_from(padded(U0, sl, s)), s.field_alloc(), s.field_alloc()])
+        t = 0.0
+        q = p.copy()
+        for i in range(steps):
+            q.iter = i; q.time = t
+            # every rank must take the same adaptive decision: step all slabs with a shared error norm
+            from bachelors_b200.slabs import step_slabs_lockstep
+            dt = step_slabs_lockstep(solvers, q, st)
+            t += dt
+            for g, (sl, s) in enumerate(zip(slabs, solvers)):
+                st[g][0], st[g][2] = st[g][2], st[g][0]
+                st[g][1], st[g][3] = st[g][3], st[g][1]
+            # halo exchange through the host (the transport is the caller's: NCCL / peer copies on a real multi-GPU run)
+            full_F = np.empty((ny, nx)); full_U = np.empty((ny, nx))
+            for sl, s, f in zip(slabs, solvers, st):
+                a = s.download(f[0]); b = s.download(f[1])
+                full_F[sl.y0:sl.y0 + sl.ny_local] = a[s.first_owned_row:s.first_owned_row + sl.ny_local]
+                full_U[sl.y0:sl.y0 + sl.ny_local] = b[s.first_owned_row:s.first_owned_row + sl.ny_local]
+            for sl, s, f in zip(slabs, solvers, st):
+                s.upload(f[0], padded(full_F, sl, s)); s.upload(f[1], padded(full_U, sl, s))
+        assert abs(t - want[2]) <= 1e-18
+        assert np.array_equal(full_F, want[0]) and np.array_equal(full_U, want[1])
+    finally:
+        for s in solvers:
+            s.close()
+
+
+# ---- full-size, size-independent properties (BASELINE.json sizes) ---------------------------------------------------------
+@pytest.mark.parametrize("solver,dtype", [("explicit", PF_F64), ("explicit-rk4", PF_F64), ("explicit-rk4", PF_F32), ("explicit-rk4-adaptive", PF_F64)])
+def test_full_size_2048_properties(solver, dtype):
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", f"config_{solver}_2048.ini"))
+    p = cfg.params
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = make_initial_conditions(cfg, npdt)
+    assert F0.shape == (2048, 2048)
+    with S.Solver(p.nx, p.ny, dtype) as s:
+        F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        Fo, Uo, done, t, info = s.run(p, F, U, tF, tU, 40)
+        gF, gU = s.download(Fo).astype(np.float64), s.download(Uo).astype(np.float64)
+    assert done == 40 and np.isfinite(gF).all() and np.isfinite(gU).all()
+    # enthalpy sum(T - L*Phi) is conserved under Neumann boundaries
+    h0 = (U0.astype(np.float64) - p.L * F0.astype(np.float64)).sum(); h1 = (gU - p.L * gF).sum()
+    assert abs(h1 - h0) <= (1e-9 if dtype == PF_F64 else 2e-3) * abs(h0), (h0, h1)
+    # mirror symmetry of the centred seed, to rounding
+    assert np.allclose(gF, gF[::-1, :], rtol=1e-6, atol=1e-9) and np.allclose(gF, gF[:, ::-1], rtol=1e-6, atol=1e-9)
+    # far from the seed nothing happened; at the seed something did
+    assert not gF[:512].any() and np.abs(gF - F0).max() > 1e-3
+    # the centre 256^2 window equals the oracle run on the whole grid's window? (local dependence: 40 steps x 4-5 stages < 256 cells)
+    if dtype == PF_F64 and solver != "explicit-rk4-adaptive":
+        w = 512
+        c0 = 1024 - w // 2
+        sub = default_params(**{k: getattr(p, k) for k, _ in p._fields_})
+        sub.nx = sub.ny = w; sub.L0 = p.L0 * w / p.nx
+        o = Oracle(PF_F64, w, w)
+        oF, oU, _, _ = o.run(sub, F0[c0:c0 + w, c0:c0 + w], U0[c0:c0 + w, c0:c0 + w], 40)
+        inner = slice(200, w - 200)
+        assert np.array_equal(oF[inner, inner], gF[c0:c0 + w, c0:c0 + w][inner, inner])
+        assert np.array_equal(oU[inner, inner], gU[c0:c0 + w, c0:c0 + w][inner, inner])
+
+
+def test_semi_implicit_1024_iteration_counts():
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", "config_semi-implicit_1024.ini"))
+    p = cfg.params
+    F0, U0 = make_initial_conditions(cfg)
+    with S.Solver(p.nx, p.ny, PF_F64) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        its = []
+        for i in range(5):
+            info = s.step(p, F, U, nF, nU)
+            its.append((info.Phi_iters, info.T_iters))
+            F, nF = nF, F; U, nU = nU, U
+        gF = s.download(F)
+    o = Oracle(PF_F64, p.nx, p.ny)
+    oF, oU, wits = F0, U0, []
+    for i in range(5):
+        oF, oU, _, info = o.step(p, oF, oU)
+        wits.append((info.Phi_iters, info.T_iters))
+    assert np.all(np.abs(np.array(its) - np.array(wits)) <= 1), (its, wits)
+    assert rel_l2(gF, oF) <= 1e-10
+
+
+# ---- libdevice ----------------------------------------------------------------------------------------------------------------
+def test_libdevice_restatement_bit_identical_on_gpu():
+    from _helpers.probe import Probe
+    from oracle import oracle
+    pr = Probe()
+    rng = np.random.default_rng(99)
+    n = 1 << 21
+    a = (rng.standard_normal(n) * 10.0 ** rng.integers(-10, 8, n)).astype(np.float32)
+    b = (rng.standard_normal(n) * 10.0 ** rng.integers(-10, 8, n)).astype(np.float32)
+    b[::17] = 0; a[::19] = 0; a[5::1001] = np.inf
+    c = rng.uniform(-200, 200, n).astype(np.float32)
+    c[::13] *= 1e4
+    for name, got, want in (("hypotf", oracle.hypotf(a, b), pr.hypotf(a, b)), ("atan2f", oracle.atan2f(a, b), pr.atan2f(a, b)),
+                            ("cosf", oracle.cosf(c), pr.cosf(c))):
+        same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+        assert same.all(), (name, int((~same).sum()), a[~same][:3], b[~same][:3], c[~same][:3])
