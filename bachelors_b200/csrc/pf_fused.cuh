@@ -168,8 +168,9 @@ k_fused_step(const FusedArgs<Real> a)
                     else if(s == 4) { nF[j] = pf_fma(kF, a.w[6], pf_fma(bF[j], a.w[5], pf_fma(aF[j], a.w[4], y0F)));   // y + tau/2 k1 - 3tau/2 k3 + 2tau k4
                                       nT[j] = pf_fma(kT, a.w[6], pf_fma(bT[j], a.w[5], pf_fma(aT[j], a.w[4], y0T)));
                                       // error combination so far: 0.2*k1 - 0.9*k3 + 0.8*k4 (simulation.cu:428)
-                                      bF[j] = pf_fma((Real) 0.8, kF, pf_fma(-(Real) 0.9, bF[j], (Real) 0.2 * aF[j]));
-                                      bT[j] = pf_fma((Real) 0.8, kT, pf_fma(-(Real) 0.9, bT[j], (Real) 0.2 * aT[j]));
+                                      // (nvcc rounds the product 0.9*k3 and fuses the rest; see oracle/pf_oracle_impl.h)
+                                      bF[j] = pf_fma((Real) 0.8, kF, pf_fma((Real) 0.2, aF[j], -((Real) 0.9 * bF[j])));
+                                      bT[j] = pf_fma((Real) 0.8, kT, pf_fma((Real) 0.2, aT[j], -((Real) 0.9 * bT[j])));
                                       aF[j] = pf_fma((Real) 4, kF, aF[j]); aT[j] = pf_fma((Real) 4, kT, aT[j]); } // k1 + 4*k4 (exact product)
                     else            { Real eF = pf_fma(-(Real) 0.1, kF, bF[j]);
                                       Real eT = pf_fma(-(Real) 0.1, kT, bT[j]);

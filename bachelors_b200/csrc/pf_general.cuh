@@ -99,7 +99,7 @@ __global__ void k_rkm_error(size_t N, const Real* __restrict__ k1, const Real* _
     Real m = 0;
     for(size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < N; i += (size_t) gridDim.x * blockDim.x)
     {
-        Real e = pf_fma(-(Real) 0.1, k5[i], pf_fma((Real) 0.8, k4[i], pf_fma(-(Real) 0.9, k3[i], (Real) 0.2 * k1[i])));
+        Real e = pf_fma(-(Real) 0.1, k5[i], pf_fma((Real) 0.8, k4[i], pf_fma((Real) 0.2, k1[i], -((Real) 0.9 * k3[i]))));
         e = e >= 0 ? e : -e;
         m = e > m ? e : m;
     }
@@ -152,7 +152,7 @@ k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __res
     const Real N_Phi = bsample(F, x, y + 1, nx, ny, F_bound);
     const Real S_Phi = bsample(F, x, y - 1, nx, ny, F_bound);
     const Real two_Phi = 2 * C_Phi;
-    const Real laplace_Phi = pf_fma((S_Phi - two_Phi) + N_Phi, k.one_over_dy2, ((W_Phi - two_Phi) + E_Phi) * k.one_over_dx2);
+    const Real laplace_Phi = pf_fma((W_Phi - two_Phi) + E_Phi, k.one_over_dx2, ((S_Phi - two_Phi) + N_Phi) * k.one_over_dy2);
     const Real f0 = C_Phi * (1 - C_Phi) * (C_Phi - (Real) 0.5);
     const Real one_minus_gamma = 1 - k.gamma;
     const Real C_T = U[i];
@@ -160,11 +160,12 @@ k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __res
     if(k.do_corrector_guess) { gx = (E_Phi - W_Phi) * k.one_over_2dx; gy = (N_Phi - S_Phi) * k.one_over_2dy; }
     else                     { gx = (E_Phi - W_Phi) / (2 * k.dx);     gy = (N_Phi - S_Phi) / (2 * k.dy); }
     const Real grad_Phi_norm = (Real) hypotf((float) gx, (float) gy);
-    Real k0, k1;
-    if(ANISO) { Real g = aniso_g<Real>(k, gx, gy); k0 = g * f0 * k.k0_factor; k1 = g * k.k1_factor; }
-    else      { k0 = f0 * k.k0_factor; k1 = k.k1_factor; }
+    Real gf0, k1;
+    if(ANISO) { Real g = aniso_g<Real>(k, gx, gy); gf0 = g * f0; k1 = g * k.k1_factor; }
+    else      { gf0 = f0; k1 = k.k1_factor; }
     const Real k2 = grad_Phi_norm * k.k2_factor;
-    const Real base = pf_fma(one_minus_gamma * k1, laplace_Phi, k0);
+    // here the reference's build rounds (1-gamma)*k1*laplace and fuses k0 = (g*f0)*k0_factor (oracle/pf_oracle_impl.h)
+    const Real base = pf_fma(gf0, k.k0_factor, (k1 * one_minus_gamma) * laplace_Phi);
     Real right, factor;
     if(k.do_corrector_guess)
     {
@@ -173,7 +174,7 @@ k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __res
         const Real N_T = bsample(U, x, y + 1, nx, ny, U_bound);
         const Real S_T = bsample(U, x, y - 1, nx, ny, U_bound);
         const Real two_T = 2 * C_T;
-        const Real laplace_T = pf_fma((S_T - two_T) + N_T, k.one_over_dy2, ((W_T - two_T) + E_T) * k.one_over_dx2);
+        const Real laplace_T = pf_fma((W_T - two_T) + E_T, k.one_over_dx2, ((S_T - two_T) + N_T) * k.one_over_dy2);
         const Real corr = pf_fma(k2, k.dt_L, (Real) 1);
         const Real inner = pf_fma(-k2, pf_fma(k.dt, laplace_T, C_T - k.Tm), base);
         right = pf_fma(k.dt / corr, inner, C_Phi);

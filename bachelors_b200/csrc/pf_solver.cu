@@ -48,7 +48,11 @@ struct pf_solver {
     int last_num_steps = 0;                 // simulation.cu:936
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
+    bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
+    int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
+    cudaStream_t aux_stream = nullptr;      // second stream: boundary rows of a slab run here while the interior runs on `stream`
+    cudaStream_t launch_stream = nullptr;   // stream the next fused launch goes to (stream or aux_stream)
     int64_t launches = 0;
     std::string err;
 
@@ -154,6 +158,7 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     PF_CREATE_CUDA(cudaSetDevice(device));
     PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_cg, 2 * sizeof(CgState)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
@@ -187,6 +192,7 @@ void pf_destroy(pf_solver* s)
     if(s->h_err) cudaFreeHost(s->h_err);
     if(s->h_cg) cudaFreeHost(s->h_cg);
     if(s->h_stats) cudaFreeHost(s->h_stats);
+    if(s->aux_stream) { cudaStreamSynchronize(s->aux_stream); cudaStreamDestroy(s->aux_stream); }
     if(s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -305,6 +311,7 @@ int pf_sync(pf_solver* s)
 }
 
 void* pf_stream(pf_solver* s) { return s ? (void*) s->stream : nullptr; }
+void* pf_aux_stream(pf_solver* s) { return s ? (void*) s->aux_stream : nullptr; }
 
 int64_t pf_kernel_launches(const pf_solver* s) { return s ? s->launches : 0; }
 
@@ -358,9 +365,11 @@ static int launch_fused_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bi
         s->smem_attr_done |= 1u << inst_bit;
     }
     const int own_rows = a.own_y1 - a.own_y0;
+    if(own_rows <= 0) return PF_OK;
+    cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
     dim3 grid((unsigned)((a.nx + TW - 1) / TW), (unsigned)((own_rows + TH - 1) / TH));
     dim3 block(G::EW, G::TY);
-    kern<<<grid, block, smem, s->stream>>>(a);
+    kern<<<grid, block, smem, stream>>>(a);
     PF_LAUNCH_CHECK(s);
     return PF_OK;
 }
@@ -389,6 +398,7 @@ static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, c
     a.nx = s->nx; a.ny_global = s->ny;
     a.row0 = s->slab.y0 - s->ghost_lo; a.rows_local = s->rows_alloc;
     a.own_y0 = s->slab.y0; a.own_y1 = s->slab.y0 + s->slab.ny_local;
+    if(s->win_y1 > s->win_y0) { a.own_y0 = std::max(a.own_y0, s->win_y0); a.own_y1 = std::min(a.own_y1, s->win_y1); }
     a.bc = p.Phi_boundary;
     a.wrap_y = (p.Phi_boundary == PF_BOUNDARY_PERIODIC && !s->slab.has_lo && !s->slab.has_hi) ? 1 : 0;
     a.k = make_consts<Real>(p);
@@ -525,7 +535,7 @@ template <typename Real>
 static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
 {
     const Real tau = (Real) tau_d;
-    PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
+    if(!s->rkm_keep_errors) PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
     if(s->rkm_fused)
     {
         FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
@@ -879,6 +889,50 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
     if(U_out) *U_out = cU;
     if(steps_done) *steps_done = i;
     if(t_advanced) *t_advanced = t - params->time;
+    return PF_OK;
+}
+
+// Scoped row window + stream selection for the *_rows_async entry points.
+struct RowWindow {
+    pf_solver* s;
+    RowWindow(pf_solver* s_, int y0, int y1, int on_aux) : s(s_) { s->win_y0 = y0; s->win_y1 = y1; s->launch_stream = on_aux ? s->aux_stream : s->stream; }
+    ~RowWindow() { s->win_y0 = s->win_y1 = 0; s->launch_stream = nullptr; }
+};
+
+int pf_step_rows_async(pf_solver* s, const pf_params* params, const void* F, const void* U, void* next_F, void* next_U,
+                       int y_begin, int y_end, int on_aux_stream)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    if(params->solver != PF_SOLVER_EXPLICIT_EULER && params->solver != PF_SOLVER_EXPLICIT_RK4)
+        return fail(s, PF_ERR_UNSUPPORTED, "pf_step_rows_async: explicit / explicit-rk4 only (use pf_rkm_attempt_rows_async for the adaptive solver)");
+    if(params->do_corrector_loop || params->do_stats || params->do_stats_step_residual || !fused_eligible(s, *params) || (s->last_num_steps % 2) != 0)
+        return fail(s, PF_ERR_UNSUPPORTED, "pf_step_rows_async: needs the fused single-kernel path (equal boundary types, no corrector loop, no statistics)");
+    if(y_end <= y_begin) return PF_OK;
+    RowWindow w(s, y_begin, y_end, on_aux_stream);
+    return s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
+                              : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
+}
+
+int pf_rkm_attempt_rows_async(pf_solver* s, const pf_params* params, double tau, const void* F, const void* U, void* next_F, void* next_U,
+                              int y_begin, int y_end, int on_aux_stream)
+{
+    if(int rc = bind(s)) return rc;
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    if(!s->rkm_fused) return fail(s, PF_ERR_UNSUPPORTED, "pf_rkm_attempt_rows_async: needs the fused path (equal boundary types)");
+    if(y_end <= y_begin) return PF_OK;
+    RowWindow w(s, y_begin, y_end, on_aux_stream);
+    s->rkm_keep_errors = true;          // the caller zeroes the error words once per attempt with pf_rkm_clear_errors_async
+    int rc = s->dtype == PF_F64 ? rkm_attempt<double>(s, *params, tau, (const double*) F, (const double*) U, (double*) next_F, (double*) next_U)
+                                : rkm_attempt<float>(s, *params, tau, (const float*) F, (const float*) U, (float*) next_F, (float*) next_U);
+    s->rkm_keep_errors = false;
+    return rc;
+}
+
+int pf_rkm_clear_errors_async(pf_solver* s, int on_aux_stream)
+{
+    if(int rc = bind(s)) return rc;
+    PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), on_aux_stream ? s->aux_stream : s->stream));
     return PF_OK;
 }
 

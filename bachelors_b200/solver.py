@@ -17,6 +17,7 @@ EXPORTS = [
     "pf_abi_version", "pf_device_count", "pf_last_error", "pf_sizeof_real", "pf_required_ghost",
     "pf_create", "pf_create_slab", "pf_destroy", "pf_reset_state",
     "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download", "pf_upload_raw", "pf_download_raw",
+    "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
     "pf_step", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
@@ -51,6 +52,10 @@ def lib():
         "pf_field_alloc": (i32, [vp, P(vp)]), "pf_field_free": (i32, [vp, vp]), "pf_field_rows": (i32, [vp, P(i32), P(i32)]),
         "pf_upload": (i32, [vp, vp, vp, sz, i32]), "pf_download": (i32, [vp, vp, vp, sz, i32]),
         "pf_upload_raw": (i32, [vp, vp, vp, sz]), "pf_download_raw": (i32, [vp, vp, vp, sz]),
+        "pf_aux_stream": (vp, [vp]),
+        "pf_step_rows_async": (i32, [vp, P(pf_params), vp, vp, vp, vp, i32, i32, i32]),
+        "pf_rkm_attempt_rows_async": (i32, [vp, P(pf_params), dbl, vp, vp, vp, vp, i32, i32, i32]),
+        "pf_rkm_clear_errors_async": (i32, [vp, i32]),
         "pf_rkm_begin": (i32, [vp, P(pf_params), vp, vp, P(dbl)]),
         "pf_rkm_attempt_async": (i32, [vp, P(pf_params), dbl, vp, vp, vp, vp]),
         "pf_rkm_error_bits": (vp, [vp]),

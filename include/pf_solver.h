@@ -185,6 +185,18 @@ PF_API int  pf_step_async(pf_solver* s, const pf_params* params,
                           const void* F, const void* U, void* next_F, void* next_U);
 PF_API int  pf_sync(pf_solver* s);
 PF_API void* pf_stream(pf_solver* s);                        /* cudaStream_t of the solver, for callers that order their own work */
+PF_API void* pf_aux_stream(pf_solver* s);                    /* second cudaStream_t: boundary rows of a slab (see *_rows_async) */
+
+/* Row-windowed variants for overlapping the halo exchange with compute: produce only the owned
+ * global rows in [y_begin, y_end), on the solver's stream or (on_aux_stream != 0) on its auxiliary stream. A slab rank
+ * launches its first/last `ghost` rows on the auxiliary stream, hands them to the transport, and launches the
+ * interior rows on the main stream meanwhile. Fused single-kernel path only (equal boundary types, no statistics). */
+PF_API int  pf_step_rows_async(pf_solver* s, const pf_params* params, const void* F, const void* U, void* next_F, void* next_U,
+                               int y_begin, int y_end, int on_aux_stream);
+PF_API int  pf_rkm_attempt_rows_async(pf_solver* s, const pf_params* params, double tau,
+                                      const void* F, const void* U, void* next_F, void* next_U,
+                                      int y_begin, int y_end, int on_aux_stream);
+PF_API int  pf_rkm_clear_errors_async(pf_solver* s, int on_aux_stream);   /* zero pf_rkm_error_bits() before the first window of an attempt */
 
 /* ---- the adaptive step in phases, for callers that own a cross-rank reduction ----
  * explicit_solver_rk4_adaptive_step (simulation.cu:350-497) = begin; { attempt; [all-reduce MAX]; decide } until stop; finish.

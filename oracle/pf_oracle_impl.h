@@ -9,9 +9,10 @@
  * The fusions written out below as explicit FMA(...) are the ones nvcc 12.9.86 makes for the
  * reference's expressions on sm_100a, read from the SASS of the reference object built by
  * oracle/build_ref.sh (cuobjdump -sass oracle/_ref/simulation_f64.o, kernel
- * cuda_tiled_for_2D_kernel<Phase_Temp, ...explicit_solver_solve_lin_combination<true,...>>): every
- * product that directly feeds an add/sub is fused, left to right. This file must be compiled with
- * -ffp-contract=off so that nothing else is fused.
+ * cuda_tiled_for_2D_kernel<Phase_Temp, ...explicit_solver_solve_lin_combination<...>>, the two
+ * semi_implicit_solver_step_based prepare kernels, the Merson error-norm reduction; fp64 and fp32 objects agree).
+ * Which product of an `a*b + c*d` is fused differs from expression to expression, so each one below is
+ * written the way the SASS has it. This file must be compiled with -ffp-contract=off so that nothing else is fused.
  */
 
 #define CAT_(a, b) a##b
@@ -118,8 +119,9 @@ static inline void FN(orc_rhs_cell)(const FN(orc_consts)* c,
     REAL g_theta = FMA(-FN(orc_custom_cos)(FMA(c->m0, theta, c->theta0)), c->S0, (REAL) 1);   /* 1 - S0*cos(m0*theta + theta0) */
 
     REAL two_Phi = 2 * C_Phi, two_T = 2 * C_T;
-    REAL laplace_Phi = FMA((S_Phi - two_Phi) + N_Phi, c->one_over_dy2, ((W_Phi - two_Phi) + E_Phi) * c->one_over_dx2);
-    REAL laplace_T   = FMA((S_T - two_T) + N_T,       c->one_over_dy2, ((W_T - two_T) + E_T) * c->one_over_dx2);
+    /* a*b + c*d: nvcc fuses the x product and rounds the y product (DMUL ysum, DFMA xsum in every RHS kernel's SASS) */
+    REAL laplace_Phi = FMA((W_Phi - two_Phi) + E_Phi, c->one_over_dx2, ((S_Phi - two_Phi) + N_Phi) * c->one_over_dy2);
+    REAL laplace_T   = FMA((W_T - two_T) + E_T,       c->one_over_dx2, ((S_T - two_T) + N_T) * c->one_over_dy2);
 
     REAL f0 = C_Phi * (1 - C_Phi) * (C_Phi - (REAL) 0.5);                  /* :129-132 */
     REAL k0 = g_theta * f0 * c->k0_factor;
@@ -284,8 +286,10 @@ static double FN(orc_rk4_adaptive_step)(orc_state* s, const pf_params* p, const 
         #pragma omp parallel for schedule(static) reduction(max:max_F) reduction(max:max_U)
         for(size_t j = 0; j < N; j++)
         {
-            REAL eF = FMA(-(REAL) 0.1, k5_F[j], FMA((REAL) 0.8, k4_F[j], FMA(-(REAL) 0.9, k3_F[j], (REAL) 0.2 * k1_F[j])));
-            REAL eU = FMA(-(REAL) 0.1, k5_U[j], FMA((REAL) 0.8, k4_U[j], FMA(-(REAL) 0.9, k3_U[j], (REAL) 0.2 * k1_U[j])));
+            /* nvcc contracts a*b - c*d + ... as fma(.., fma(.., fma(0.2, k1, -(0.9*k3)))): the rounded product is 0.9*k3
+             * (SASS of cuda_produce_reduce_kernel<Reduce::Max, ..., explicit_solver_rk4_adaptive_step lambda>: DMUL k3, DFMA k1, DFMA k4, DFMA k5) */
+            REAL eF = FMA(-(REAL) 0.1, k5_F[j], FMA((REAL) 0.8, k4_F[j], FMA((REAL) 0.2, k1_F[j], -((REAL) 0.9 * k3_F[j]))));
+            REAL eU = FMA(-(REAL) 0.1, k5_U[j], FMA((REAL) 0.8, k4_U[j], FMA((REAL) 0.2, k1_U[j], -((REAL) 0.9 * k3_U[j]))));
             eF = eF >= 0 ? eF : -eF;
             eU = eU >= 0 ? eU : -eU;
             if(eF > max_F) max_F = eF;
@@ -499,7 +503,7 @@ static void FN(orc_semi_implicit_step_based)(orc_state* s, const pf_params* p, c
             REAL N_Phi = FN(orc_boundary_sample)(F, x, y + 1, nx, ny, c.F_bound);
             REAL S_Phi = FN(orc_boundary_sample)(F, x, y - 1, nx, ny, c.F_bound);
             REAL two_Phi = 2 * C_Phi;
-            REAL laplace_Phi = FMA((S_Phi - two_Phi) + N_Phi, c.one_over_dy2, ((W_Phi - two_Phi) + E_Phi) * c.one_over_dx2);
+            REAL laplace_Phi = FMA((W_Phi - two_Phi) + E_Phi, c.one_over_dx2, ((S_Phi - two_Phi) + N_Phi) * c.one_over_dy2);
             REAL f0 = C_Phi * (1 - C_Phi) * (C_Phi - (REAL) 0.5);
             if(c.do_corrector_guess)
             {
@@ -515,12 +519,13 @@ static void FN(orc_semi_implicit_step_based)(orc_state* s, const pf_params* p, c
                 REAL theta = FN(orc_custom_atan2)(grad_Phi_y, grad_Phi_x);
                 REAL g_theta = FMA(-FN(orc_custom_cos)(FMA(c.m0, theta, c.theta0)), c.S0, (REAL) 1);
                 REAL two_T = 2 * C_T;
-                REAL laplace_T = FMA((S_T - two_T) + N_T, c.one_over_dy2, ((W_T - two_T) + E_T) * c.one_over_dx2);
-                REAL k0 = g_theta * f0 * c.k0_factor;
+                REAL laplace_T = FMA((W_T - two_T) + E_T, c.one_over_dx2, ((S_T - two_T) + N_T) * c.one_over_dy2);
+                /* (1-gamma)*k1*laplace + k0: here nvcc rounds the first product and fuses k0 = (g*f0)*k0_factor
+                 * (SASS of the two prepare kernels: DMUL lap*(k1*(1-gamma)), DFMA (g*f0)*k0_factor + that) */
                 REAL k2 = grad_Phi_norm * c.k2_factor;
                 REAL k1 = g_theta * c.k1_factor;
                 REAL corr = FMA(k2, c.dt_L, (REAL) 1);
-                REAL inner = FMA(-k2, FMA(dt, laplace_T, C_T - Tm), FMA(one_minus_gamma * k1, laplace_Phi, k0));
+                REAL inner = FMA(-k2, FMA(dt, laplace_T, C_T - Tm), FMA(g_theta * f0, c.k0_factor, (k1 * one_minus_gamma) * laplace_Phi));
                 REAL right = FMA(dt / corr, inner, C_Phi);                  /* :828 */
                 REAL factor = gamma / corr * k1;                            /* :829 */
                 anisotropy[i] = factor;
@@ -535,10 +540,9 @@ static void FN(orc_semi_implicit_step_based)(orc_state* s, const pf_params* p, c
                 REAL grad_Phi_norm = FN(orc_custom_hypot)(grad_Phi_x, grad_Phi_y);
                 REAL theta = FN(orc_custom_atan2)(grad_Phi_y, grad_Phi_x);
                 REAL g_theta = FMA(-FN(orc_custom_cos)(FMA(c.m0, theta, c.theta0)), c.S0, (REAL) 1);
-                REAL k0 = g_theta * f0 * c.k0_factor;
                 REAL k2 = grad_Phi_norm * c.k2_factor;
                 REAL k1 = g_theta * c.k1_factor;
-                REAL inner = FMA(-k2, C_T - Tm, FMA(one_minus_gamma * k1, laplace_Phi, k0));
+                REAL inner = FMA(-k2, C_T - Tm, FMA(g_theta * f0, c.k0_factor, (k1 * one_minus_gamma) * laplace_Phi));
                 REAL right = FMA(dt, inner, C_Phi);                         /* :864 */
                 REAL factor = gamma * k1;                                   /* :865 */
                 anisotropy[i] = factor;
