@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: GLUPS (1e9 cell updates per second) of one time step of the phase-field solver.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--solver explicit-rk4] [--dtype f64]
+
+N = 1: workload = benchmark_configs/config_<solver>_2048.ini (default explicit-rk4: BASELINE.json's metric config), fp64.
+N > 1 (launched by torchrun, one rank per GPU): the 16384-wide synthetic family of BASELINE.json configs[4], cut into
+y-slabs of 2048 rows per GPU (16384 x 2048*N cells; N = 8 is the 16384^2 grid), weak scaling, halo exchange over NCCL.
+A "step" is one time step of the solver over the whole grid. Synthetic data: the config's own dendrite seed.
+
+One JSON line on stdout (rank 0). See DESIGN.md "Measurement" for how every key is produced.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from bachelors_b200._abi import PF_F32, PF_F64, SOLVER_NAMES                # noqa: E402
+from bachelors_b200.config import read_config                               # noqa: E402
+from bachelors_b200.initial import make_initial_conditions                  # noqa: E402
+
+PER_GPU_ROWS = 2048
+WIDE_NX = 16384
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def load_traffic(solver, dtype_name):
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/traffic.json), or None."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f).get(f"{solver}_{dtype_name}_2048")
+    return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def finish(self):
+        self._stop.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_gpu_index(local):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local])
+        except Exception:
+            return local
+    return local
+
+
+def workload(args, world):
+    """-> (cfg, description). The config file supplies every parameter; for N > 1 only the grid is widened."""
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", f"config_{args.solver}_2048.ini"))
+    if world == 1 and not args.wide:
+        return cfg, f"config_{args.solver}_2048.ini ({args.dtype})"
+    p = cfg.params
+    dx = p.L0 / p.nx
+    p.nx, p.ny = WIDE_NX, PER_GPU_ROWS * world
+    # the reference has one L0 for both axes (dx = L0/nx, dy = L0/ny); keep dx = 4/512 and let dy follow
+    p.L0 = dx * p.nx
+    cfg.init_circle_center = (p.L0 / 2, p.L0 / 2)
+    return cfg, f"synthetic {args.solver} {p.nx}x{p.ny} ({args.dtype}), {PER_GPU_ROWS}-row slab per GPU"
+
+
+# ------------------------------------------------------------------------------------------------------------------------------
+# reference arm: the CPU oracle port (the reference has no CPU implementation of this path, see DESIGN.md "Oracle")
+# ------------------------------------------------------------------------------------------------------------------------------
+def cpu_window(cfg, dtype, w):
+    """A centred w x w window of the workload as its own grid with L0 scaled by w/nx: dx, dy and therefore every cell's
+    arithmetic are those of the full grid (a bounded sample of the same workload)."""
+    p = cfg.params.copy()
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = make_initial_conditions(cfg, npdt)
+    if w and w < min(p.nx, p.ny):
+        x0, y0 = (p.nx - w) // 2, (p.ny - w) // 2
+        F0 = np.ascontiguousarray(F0[y0:y0 + w, x0:x0 + w]); U0 = np.ascontiguousarray(U0[y0:y0 + w, x0:x0 + w])
+        p.L0 = p.L0 * w / p.nx
+        p.nx = p.ny = w
+    return p, F0, U0
+
+
+def cpu_port_rate(cfg, dtype, budget_s, max_steps, w=None):
+    """Times oracle steps on the host cores. -> (GLUPS, cores, sample text)."""
+    from oracle.oracle import Oracle, lib as olib
+    cores = olib().orc_max_threads()
+    p, F, U = cpu_window(cfg, dtype, w)
+    o = Oracle(dtype, p.nx, p.ny)
+    F, U, _, _ = o.step(p, F, U)                     # warm-up (allocates the oracle's scratch fields)
+    n, t0 = 0, time.perf_counter()
+    while n < max_steps and (time.perf_counter() - t0) < budget_s:
+        F, U, _, _ = o.step(p, F, U)
+        n += 1
+    secs = time.perf_counter() - t0
+    sample = f"{n} step(s) of {p.nx}x{p.ny} {('fp64' if dtype == PF_F64 else 'fp32')} in {secs:.1f} s on {cores} OpenMP thread(s)"
+    return p.nx * p.ny * n / secs / 1e9, cores, sample
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return 0
+    dtype = PF_F64 if args.dtype == "f64" else PF_F32
+    cfg, desc = workload(args, 1)
+    # bounded sample per step: a centred 724^2 window (1/8 of the 2048^2 cells, same dx/dy) so that K steps end within minutes
+    w = 724
+    from oracle.oracle import Oracle, lib as olib
+    cores = olib().orc_max_threads()
+    p, F, U = cpu_window(cfg, dtype, w)
+    o = Oracle(dtype, p.nx, p.ny)
+    for _ in range(max(args.warmup, 1)):
+        F, U, _, _ = o.step(p, F, U)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        F, U, _, _ = o.step(p, F, U)
+    secs = time.perf_counter() - t0
+    glups = p.nx * p.ny * args.steps / secs / 1e9
+    sample = f"each step = one {args.solver} step on the centred {w}x{w} window of the 2048^2 dendrite config (same dx, dy), {cores} OpenMP threads"
+    line = {
+        "impl": "reference", "metric": "GLUPS", "value": glups, "unit": "1e9 cell updates/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic (config's dendrite seed)",
+        "config": {"workload": desc, "solver": args.solver, "note": "the reference has no CPU implementation of this path (CUDA only); "
+                   "this arm times the CPU oracle port of it (oracle/, C + OpenMP) on the host cores"},
+        "cpu_baseline": {"value": glups, "unit": "1e9 cell updates/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------------------------------------
+# the CUDA arm
+# ------------------------------------------------------------------------------------------------------------------------------
+def time_device_steps(runner, torch, steps, world, dist):
+    """K steps bracketed by barrier + synchronize, timed with CUDA events on the solver's stream; max over ranks."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    runner.sync()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record(runner.main)
+    t_adv, attempts = 0.0, 0
+    for _ in range(steps):
+        t_adv += runner.step()
+        attempts += runner.last_attempts
+    # the step's tail may live on the aux / comm streams: make main wait for them before the closing event
+    runner.main.wait_event(runner.ev_aux)
+    runner.main.wait_event(runner.ev_halo)
+    e1.record(runner.main)
+    runner.sync()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    return ms, t_adv, attempts
+
+
+def time_e2e(runner, torch, steps, world, dist):
+    """The reference-facing call sequence with HOST buffers: every step uploads (Phi, T) from pinned host memory
+    (sim_modify UPLOAD), steps once (sim_step, which returns after a device synchronisation, simulation.cu:1153) and
+    downloads the result (sim_modify DOWNLOAD). Wall clock bracketed by synchronize; max over ranks."""
+    own_F, own_U = runner.owned(runner.F), runner.owned(runner.U)
+    hF = torch.empty(own_F.shape, dtype=own_F.dtype).pin_memory()
+    hU = torch.empty(own_U.shape, dtype=own_U.dtype).pin_memory()
+    hF.copy_(own_F); hU.copy_(own_U)
+    nbytes = hF.numel() * hF.element_size() * 2
+    s, L = runner.solver, None
+    from bachelors_b200 import solver as S
+    L = S.lib()
+    dt_code = runner.dtype
+    runner.sync()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        s._ck(L.pf_upload(s._h, runner.owned(runner.F).data_ptr(), hF.data_ptr(), hF.numel(), dt_code))
+        s._ck(L.pf_upload(s._h, runner.owned(runner.U).data_ptr(), hU.data_ptr(), hU.numel(), dt_code))
+        if world > 1:
+            runner.exchange(runner.F, runner.U)          # the uploaded rows' halos (host data changed the owned rows)
+        runner.step()
+        runner.sync()
+        s._ck(L.pf_download(s._h, runner.owned(runner.F).data_ptr(), hF.data_ptr(), hF.numel(), dt_code))
+        s._ck(L.pf_download(s._h, runner.owned(runner.U).data_ptr(), hU.data_ptr(), hU.numel(), dt_code))
+    torch.cuda.synchronize()
+    secs = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([secs], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = float(t.item())
+    return secs, nbytes, nbytes
+
+
+def run_cuda_arm(args):
+    import torch
+    import torch.distributed as dist
+    from bachelors_b200 import solver as S
+    from bachelors_b200.distributed import SlabRunner
+    from bachelors_b200.slabs import slab_rows
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch N > 1 with torch.distributed.run (one rank per GPU)")
+    S.lib()                                             # fails loudly if the CUDA library is missing
+    if not torch.cuda.is_available():
+        raise SystemExit("no CUDA device: this benchmark has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dtype = PF_F64 if args.dtype == "f64" else PF_F32
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    cfg, desc = workload(args, world)
+    p = cfg.params
+    y0, y1 = slab_rows(p.ny, world, rank)
+    F0, U0 = make_initial_conditions(cfg, npdt, rows=(y0, y1))
+
+    runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap)
+    runner.upload_global(F0, U0)
+    launches0 = runner.solver.kernel_launches
+    for _ in range(args.warmup):
+        runner.step()
+    runner.sync()
+
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
+    launches1 = runner.solver.kernel_launches
+    ms, t_adv, attempts = time_device_steps(runner, torch, args.steps, world, dist)
+    launches = runner.solver.kernel_launches - launches1
+    clocks = sampler.finish()
+
+    cells = p.nx * p.ny
+    glups = cells * args.steps / (ms * 1e-3) / 1e9
+    rs = 8 if dtype == PF_F64 else 4
+    peak, peak_src = load_peaks()
+    # dominant kernel: the fused step kernel, one launch per step (adaptive: one per attempt) producing this rank's rows
+    launches_per_step = launches / args.steps
+    alg_bytes_per_launch = 4 * rs * (cells / world)                    # read Phi, T + write Phi', T' 
+    avg_launch_s = (ms * 1e-3) / max(attempts if args.solver == "explicit-rk4-adaptive" else args.steps, 1)
+    achieved = alg_bytes_per_launch / avg_launch_s / 1e9
+    traffic = load_traffic(args.solver, args.dtype) if world == 1 and not args.wide else None
+
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    e2e_secs, h2d, d2h = time_e2e(runner, torch, e2e_steps, world, dist)
+    e2e_glups = cells * e2e_steps / e2e_secs / 1e9
+
+    tot_launches = launches
+    if world > 1:
+        t = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        tot_launches = int(t.item())
+
+    line = {
+        "metric": "GLUPS", "value": glups, "unit": "1e9 cell updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic (config's dendrite seed; no dataset)",
+        "config": {"workload": desc, "solver": args.solver, "nx": p.nx, "ny": p.ny, "parallelism": f"y-slabs x{world}",
+                   "l2_policy": ("working set (2 fields in + 2 out) %.0f MB per GPU vs 126 MB L2; consecutive time steps, no flush"
+                                 % (4 * rs * cells / world / 1e6)),
+                   "halo_overlap": (not args.no_overlap) if world > 1 else None},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "kernel": "k_fused_step", "peak_source": peak_src,
+                     "algorithmic_bytes_per_cell_step": 4 * rs, "launches_per_step": launches_per_step},
+        "e2e": {"value": e2e_glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
+                "steps": e2e_steps, "what": "pf_upload(Phi,T) from pinned host + pf_step + pf_download(Phi,T) every step"},
+        "gpu_launches": tot_launches,
+        "clocks": clocks,
+        "sim_time_advanced": t_adv,
+    }
+    if args.solver == "explicit-rk4-adaptive":
+        line["attempts_per_step"] = attempts / args.steps
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        v, cores, sample = cpu_port_rate(cfg, dtype, budget_s=args.cpu_budget, max_steps=40, w=None if not args.wide else 2048)
+        line["cpu_baseline"] = {"value": v, "unit": "1e9 cell updates/s", "cores": cores, "kind": "port", "sample": sample}
+    if rank == 0 and world == 1 and not args.no_ref_gpu:
+        ref = same_box_reference(cfg, dtype, args)
+        if ref:
+            line["reference_gpu_same_box"] = ref
+    runner.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+def same_box_reference(cfg, dtype, args):
+    """The UNMODIFIED reference kernels (oracle/_ref, built for sm_100a) timed on the same GPU: 'the kernel to beat'.
+    Extra information only; never part of `value`."""
+    try:
+        from oracle import ref_sim
+        if not ref_sim.available(dtype):
+            return None
+        p = cfg.params
+        npdt = np.float64 if dtype == PF_F64 else np.float32
+        F0, U0 = make_initial_conditions(cfg, npdt)
+        with ref_sim.RefSim(dtype, p.nx, p.ny, fresh=True) as ref:
+            ref.upload(F0, U0)
+            ref.time_ms(p, 3)
+            n = 20
+            ms, _ = ref.time_ms(p, n)
+        return {"ms_per_step": ms / n, "value": p.nx * p.ny * n / (ms * 1e-3) / 1e9, "unit": "1e9 cell updates/s",
+                "what": "reference simulation.cu compiled unmodified for sm_100a, same config, CUDA events around sim_step calls"}
+    except Exception as e:                                   # never let the extra leg break the bench line
+        return {"error": str(e)[:200]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--solver", default="explicit-rk4", choices=[k for k in SOLVER_NAMES if k not in ("none", "exact", "semi-implicit")])
+    ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
+    ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=12.0)
+    ap.add_argument("--e2e-steps", type=int, default=20)
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_cuda_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,88 @@
+"""SlabRunner (bachelors_b200/distributed.py) on real devices: world size 1 in-process, world size 2 under torchrun when
+the box has two GPUs. The slabs must reproduce the single-grid CUDA result bit for bit."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from bachelors_b200 import solver as S
+from bachelors_b200._abi import PF_F64, default_params
+from bachelors_b200.testing import seeded_fields
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+WORKER = r'''
+import os, sys, json
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from bachelors_b200._abi import PF_F64, default_params
+from bachelors_b200.testing import seeded_fields
+from bachelors_b200.distributed import SlabRunner
+from bachelors_b200.slabs import slab_rows
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+solver, bc, nx, ny, steps, out = sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5]), int(sys.argv[6]), sys.argv[7]
+p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_boundary=bc, T_boundary=bc, Phi_tolerance=1e-7, T_tolerance=1e-7)
+F0, U0 = seeded_fields(nx, ny, kind="interface")
+y0, y1 = slab_rows(ny, world, rank)
+r = SlabRunner(p, PF_F64, rank=rank, world=world, device=local)
+r.upload_global(F0[y0:y1], U0[y0:y1])
+t = 0.0
+for _ in range(steps):
+    t += r.step()
+F, U = r.download_owned()
+np.savez(os.path.join(out, f"r{rank}.npz"), F=F, U=U, y0=y0, t=t)
+r.close()
+dist.barrier(); dist.destroy_process_group()
+'''
+
+
+def single_grid(solver, bc, nx, ny, steps):
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_boundary=bc, T_boundary=bc, Phi_tolerance=1e-7, T_tolerance=1e-7)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        Fo, Uo, done, t, _ = s.run(p, F, U, tF, tU, steps)
+        return s.download(Fo), s.download(Uo), t
+
+
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive"])
+def test_slab_runner_world1_equals_solver(solver):
+    import torch
+    from bachelors_b200.distributed import SlabRunner
+    nx, ny, steps = 300, 200, 5
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_tolerance=1e-7, T_tolerance=1e-7)
+    F0, U0 = seeded_fields(nx, ny, kind="interface")
+    r = SlabRunner(p, PF_F64, rank=0, world=1, device=0)
+    r.upload_global(F0, U0)
+    t = sum(r.step() for _ in range(steps))
+    F, U = r.download_owned()
+    r.close()
+    wF, wU, wt = single_grid(solver, "neumann", nx, ny, steps)
+    assert np.array_equal(F, wF) and np.array_equal(U, wU) and abs(t - wt) < 1e-18
+
+
+@pytest.mark.parametrize("solver,bc", [("explicit", "neumann"), ("explicit-rk4", "neumann"), ("explicit-rk4", "periodic"),
+                                       ("explicit-rk4-adaptive", "neumann"), ("explicit-rk4-adaptive", "periodic")])
+def test_slab_runner_two_gpus(tmp_path, solver, bc):
+    if S.lib().pf_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    nx, ny, steps = 520, 301, 6
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", str(script), ROOT, solver, bc, str(nx), str(ny), str(steps), str(tmp_path)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-3000:]
+    wF, wU, wt = single_grid(solver, bc, nx, ny, steps)
+    for r in range(2):
+        z = np.load(tmp_path / f"r{r}.npz")
+        y0 = int(z["y0"])
+        assert np.array_equal(z["F"], wF[y0:y0 + z["F"].shape[0]]), (solver, bc, r)
+        assert np.array_equal(z["U"], wU[y0:y0 + z["U"].shape[0]])
+        assert abs(float(z["t"]) - wt) < 1e-18
