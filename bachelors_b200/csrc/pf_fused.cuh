@@ -47,70 +47,33 @@ struct FusedArgs {
 
 template <int SCHEME> struct SchemeStages { static constexpr int value = SCHEME == SCHEME_EULER ? 1 : (SCHEME == SCHEME_RK4 ? 4 : 5); };
 
-template <typename Real, int SCHEME, bool ANISO, int EW, int TY, int R>
-__global__ void __launch_bounds__(EW * TY, 1)
-k_fused_step(const FusedArgs<Real> a)
+// The stage loop. FAST = the extended tile lies strictly inside the domain and inside the local rows, and no y(n)
+// value of the tile is -0: then every cell is computed unconditionally (cells in the shrinking rim hold garbage that
+// never reaches a valid cell), there is no boundary logic, and canon_zero(y) == y. Otherwise the general form runs.
+// Both forms evaluate the identical arithmetic on every valid cell.
+template <typename Real, int SCHEME, bool ANISO, int EW, int TY, int R, bool FAST>
+__device__ __forceinline__ void fused_stages(const FusedArgs<Real>& a, typename Vec2T<Real>::type* const buf0, typename Vec2T<Real>::type* const buf1,
+    const int cx, const int ry0, const int gx, const int gy0, const unsigned in_mask,
+    const Real (&yF)[R], const Real (&yT)[R], Real (&cF)[R], Real (&cT)[R], Real (&bF)[R], Real (&bT)[R])
 {
     constexpr int NST = SchemeStages<SCHEME>::value;
-    constexpr int H = NST;
     constexpr int EH = TY * R;
     using V2 = typename Vec2T<Real>::type;
-    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
-    V2* const buf0 = reinterpret_cast<V2*>(pf_smem_raw);
-    V2* const buf1 = buf0 + EW * EH;
-
-    const int cx = threadIdx.x;
-    const int ry0 = threadIdx.y * R;
     const int nx = a.nx, NY = a.ny_global;
     const int bc = a.bc;
     const bool periodic = bc == PF_BOUNDARY_PERIODIC;
-
-    const int gx = (int) blockIdx.x * (EW - 2 * H) - H + cx;
-    const int gy0 = a.own_y0 + (int) blockIdx.y * (EH - 2 * H) - H + ry0;
-
-    int lx; bool x_in;
-    if(periodic) { lx = gx % nx; if(lx < 0) lx += nx; x_in = true; }
-    else         { x_in = gx >= 0 && gx < nx; lx = gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx); }
     const bool x_lo_edge = !periodic && gx == 0;
     const bool x_hi_edge = !periodic && gx == nx - 1;
-
-    Real yF[R], yT[R];      // raw y(n)
-    Real cF[R], cT[R];      // this thread's stage inputs
     Real aF[R], aT[R];      // running combination (RK4: k1+2k2+2k3; RKM: k1, later k1+4k4)
-    Real bF[R], bT[R];      // RKM only: k3, later the error combination
-    unsigned in_mask = 0;
-
     #pragma unroll
-    for(int j = 0; j < R; j++)
-    {
-        const int gy = gy0 + j;
-        int ly; bool y_in;
-        if(a.wrap_y) { ly = gy % NY; if(ly < 0) ly += NY; y_in = true; }
-        else         { ly = gy - a.row0; y_in = ly >= 0 && ly < a.rows_local && (periodic || (gy >= 0 && gy < NY)); }
-        const bool in = x_in && y_in;
-        Real f = 0, u = 0;
-        if(in)
-        {
-            const size_t idx = (size_t) ly * (size_t) nx + (size_t) lx;
-            f = a.F[idx]; u = a.U[idx];
-            in_mask |= 1u << j;
-        }
-        yF[j] = f; yT[j] = u;
-        cF[j] = canon_zero(f); cT[j] = canon_zero(u);
-        aF[j] = aT[j] = bF[j] = bT[j] = 0;
-        V2 v; v.x = cF[j]; v.y = cT[j];
-        buf0[(ry0 + j) * EW + cx] = v;
-    }
-    __syncthreads();
-
-    Real err_F = 0, err_T = 0;
+    for(int j = 0; j < R; j++) { aF[j] = 0; aT[j] = 0; }
 
     #pragma unroll
     for(int s = 1; s <= NST; s++)
     {
         const V2* rb = (s & 1) ? buf0 : buf1;
         V2* wb = (s & 1) ? buf1 : buf0;
-        const bool col_ok = cx >= s && cx < EW - s;
+        const bool col_ok = FAST ? true : (cx >= s && cx < EW - s);
         Real nF[R], nT[R];
         #pragma unroll
         for(int j = 0; j < R; j++)
@@ -118,7 +81,7 @@ k_fused_step(const FusedArgs<Real> a)
             nF[j] = cF[j]; nT[j] = cT[j];
             const int ry = ry0 + j;
             const bool row_ok = ry >= s && ry < EH - s;          // warp-uniform
-            if(row_ok && col_ok && ((in_mask >> j) & 1u))
+            if(row_ok && (FAST || (col_ok && ((in_mask >> j) & 1u))))
             {
                 const Real CF = cF[j], CT = cT[j];
                 V2 e = rb[ry * EW + cx + 1];
@@ -126,7 +89,7 @@ k_fused_step(const FusedArgs<Real> a)
                 Real NF, NT, SF, ST;
                 if(j < R - 1) { NF = cF[j + 1]; NT = cT[j + 1]; } else { V2 n = rb[(ry + 1) * EW + cx]; NF = n.x; NT = n.y; }
                 if(j > 0)     { SF = cF[j - 1]; ST = cT[j - 1]; } else { V2 q = rb[(ry - 1) * EW + cx]; SF = q.x; ST = q.y; }
-                if(!periodic)
+                if(!FAST && !periodic)
                 {
                     const int gy = gy0 + j;
                     if(x_hi_edge)    { e.x = ghost_of(CF, bc); e.y = ghost_of(CT, bc); }
@@ -137,7 +100,7 @@ k_fused_step(const FusedArgs<Real> a)
                 Real kF, kT;
                 rhs_cell<Real, ANISO>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);
 
-                const Real y0F = canon_zero(yF[j]), y0T = canon_zero(yT[j]);
+                const Real y0F = FAST ? yF[j] : canon_zero(yF[j]), y0T = FAST ? yT[j] : canon_zero(yT[j]);
                 if(SCHEME == SCHEME_EULER)
                 {
                     // simulation.cu:233-234: C + dt*k, C being the gathered (blended) value
@@ -190,8 +153,100 @@ k_fused_step(const FusedArgs<Real> a)
         for(int j = 0; j < R; j++) { cF[j] = nF[j]; cT[j] = nT[j]; }
         if(s < NST) __syncthreads();
     }
+}
+
+template <typename Real, int SCHEME, bool ANISO, int EW, int TY, int R>
+__global__ void __launch_bounds__(EW * TY, 1)
+k_fused_step(const FusedArgs<Real> a)
+{
+    constexpr int NST = SchemeStages<SCHEME>::value;
+    constexpr int H = NST;
+    constexpr int EH = TY * R;
+    using V2 = typename Vec2T<Real>::type;
+    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
+    // one pad element in front and behind each tile: the FAST form reads cx-1 / cx+1 at the tile's corner cells
+    V2* const buf0 = reinterpret_cast<V2*>(pf_smem_raw) + 1;
+    V2* const buf1 = buf0 + EW * EH + 2;
+
+    const int cx = threadIdx.x;
+    const int ry0 = threadIdx.y * R;
+    const int nx = a.nx, NY = a.ny_global;
+    const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
+
+    const int tile_x0 = (int) blockIdx.x * (EW - 2 * H) - H;
+    const int tile_y0 = a.own_y0 + (int) blockIdx.y * (EH - 2 * H) - H;
+    const int gx = tile_x0 + cx;
+    const int gy0 = tile_y0 + ry0;
+
+    // block-uniform: the whole extended tile is inside the domain and inside this rank's rows, no wrap anywhere
+    const bool interior = tile_x0 >= 0 && tile_x0 + EW <= nx && tile_y0 >= 0 && tile_y0 + EH <= NY &&
+                          tile_y0 - a.row0 >= 0 && tile_y0 - a.row0 + EH <= a.rows_local;
+
+    Real yF[R], yT[R];      // raw y(n)
+    Real cF[R], cT[R];      // this thread's stage inputs
+    Real bF[R], bT[R];      // RKM only: k3, later the error combination
+    unsigned in_mask = 0;
+    int lx = gx;
+    bool fast = false;
+
+    if(interior)
+    {
+        int negzero = 0;
+        const size_t base = (size_t)(gy0 - a.row0) * (size_t) nx + (size_t) gx;
+        #pragma unroll
+        for(int j = 0; j < R; j++)
+        {
+            const Real f = a.F[base + (size_t) j * (size_t) nx], u = a.U[base + (size_t) j * (size_t) nx];
+            yF[j] = f; yT[j] = u;
+            bF[j] = bT[j] = 0;
+        }
+        // -0 compares equal to +0, so test the bit patterns
+        #pragma unroll
+        for(int j = 0; j < R; j++) negzero |= (int) is_negzero(yF[j]) | (int) is_negzero(yT[j]);
+        #pragma unroll
+        for(int j = 0; j < R; j++)
+        {
+            cF[j] = canon_zero(yF[j]); cT[j] = canon_zero(yT[j]);
+            V2 v; v.x = cF[j]; v.y = cT[j];
+            buf0[(ry0 + j) * EW + cx] = v;
+        }
+        in_mask = (1u << R) - 1u;
+        fast = __syncthreads_or(negzero) == 0;
+    }
+    else
+    {
+        bool x_in;
+        if(periodic) { lx = gx % nx; if(lx < 0) lx += nx; x_in = true; }
+        else         { x_in = gx >= 0 && gx < nx; lx = gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx); }
+        #pragma unroll
+        for(int j = 0; j < R; j++)
+        {
+            const int gy = gy0 + j;
+            int ly; bool y_in;
+            if(a.wrap_y) { ly = gy % NY; if(ly < 0) ly += NY; y_in = true; }
+            else         { ly = gy - a.row0; y_in = ly >= 0 && ly < a.rows_local && (periodic || (gy >= 0 && gy < NY)); }
+            const bool in = x_in && y_in;
+            Real f = 0, u = 0;
+            if(in)
+            {
+                const size_t idx = (size_t) ly * (size_t) nx + (size_t) lx;
+                f = a.F[idx]; u = a.U[idx];
+                in_mask |= 1u << j;
+            }
+            yF[j] = f; yT[j] = u;
+            cF[j] = canon_zero(f); cT[j] = canon_zero(u);
+            bF[j] = bT[j] = 0;
+            V2 v; v.x = cF[j]; v.y = cT[j];
+            buf0[(ry0 + j) * EW + cx] = v;
+        }
+        __syncthreads();
+    }
+
+    if(fast) fused_stages<Real, SCHEME, ANISO, EW, TY, R, true>(a, buf0, buf1, cx, ry0, gx, gy0, in_mask, yF, yT, cF, cT, bF, bT);
+    else     fused_stages<Real, SCHEME, ANISO, EW, TY, R, false>(a, buf0, buf1, cx, ry0, gx, gy0, in_mask, yF, yT, cF, cT, bF, bT);
 
     // write the interior: cF/cT now hold y(n+1) for every cell that survived all H stages
+    Real err_F = 0, err_T = 0;
     const bool col_int = cx >= H && cx < EW - H;
     #pragma unroll
     for(int j = 0; j < R; j++)

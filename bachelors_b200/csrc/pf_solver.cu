@@ -357,7 +357,7 @@ static int launch_fused_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bi
     constexpr int TW = G::EW - 2 * NST, TH = EH - 2 * NST;
     static_assert(TW > 0 && TH > 0, "tile too small for the stage count");
     using V2 = typename Vec2T<Real>::type;
-    const size_t smem = sizeof(V2) * (size_t) G::EW * EH * (NST > 1 ? 2 : 1);
+    const size_t smem = sizeof(V2) * ((size_t) G::EW * EH + 2) * 2;      // two tiles, one pad element at each end of both
     auto kern = k_fused_step<Real, SCHEME, ANISO, G::EW, G::TY, G::R>;
     if(!(s->smem_attr_done & (1u << inst_bit)))
     {
