@@ -1,0 +1,418 @@
+// pf_stream.cuh - streaming temporally blocked explicit integrators: ALL stages of one time step in ONE kernel,
+// marching down the rows with a skewed software pipeline.
+//
+// Replaces, for one time step, the reference's 1 (Euler) / 5 (RK4) / >=7 (Merson) launches of
+// explicit_solver_solve_lin_combination + combine + reductions (reference simulation.cu:283-497).
+//
+// One CTA of EW = 32*WARPS threads owns a column strip: thread cx owns global column gx = strip_x0 - H + cx
+// (H = #stages; the H columns on each side are halo) and walks down a chunk of rows. In iteration `it` the thread
+// evaluates stage s on row g1 - SK*(s-1), g1 = G0 + it being the row of stage 1 and SK the skew:
+//   SK = 1: stage s+1 consumes, as its N neighbour, what stage s has produced in the same iteration (least state,
+//           but the stages of one row form one dependency chain);
+//   SK = 2: everything a stage consumes was produced in EARLIER iterations, so the NST stage evaluations of an
+//           iteration are independent instruction streams the scheduler can interleave (the kernel is bound by
+//           the latency of the FP64 / float-hypot chain, not by issue slots or bytes).
+// The N/S neighbours and the running combinations of the k's live in REGISTERS (rings indexed by row modulo U,
+// U = SK + 2 = the unroll factor, all indices compile-time). Shared memory carries (i) the E/W neighbours: one row
+// of {Phi,T} pairs per stage in a U-deep ring, and (ii) a ring of the last YR rows of canon_zero(y(n)), from which
+// stage 1 takes its E/W neighbours and stages >= 2 re-read their own column's y instead of holding it in registers.
+// ONE __syncthreads per row. y(n) is read from global memory once per strip (two rows ahead of its use) and y(n+1)
+// is written once: HBM traffic per cell per step = read {Phi,T} + write {Phi,T} = 4 reals (x EW/(EW-2H) strip
+// overlap, served by L2), the algorithmic minimum. Redundant arithmetic: EW/(EW-2H) in x; in y
+// only the pipeline fill (stage s idles for the first (SK+1)(s-1) iterations of a chunk) - no 2-D halo recomputation.
+//
+// Garbage discipline: halo columns and out-of-domain rows are computed from clamped loads; wrong values move inward
+// one cell per stage, so after NST stages exactly the interior columns are clean, and at non-periodic edges the
+// ghost rule below overrides every arm that points outside before it can reach a valid cell.
+//
+// Boundaries: when a stencil arm of an edge cell points outside a non-periodic edge, the ghost value of
+// boundary_sample (reference simulation.cu:33-85) is formed from the edge cell's own stage input (Neumann: same
+// value, Dirichlet: 0 - value) - the reference applies boundary_sample to every blended state, and the blend is
+// linear. In x the edge thread itself stores that ghost pair into the exchange slot of the column outside (whose
+// own thread does not store), so the stencil code has no x-boundary logic at all. In y the ghost replaces the N/S
+// register operand, which only happens in the `CHECKED` form of the loop body: iterations are grouped by U, and a
+// group runs the straight-line form (no activity tests, no boundary selects, one basic block per row) whenever all
+// stages are active and no stage row is a domain edge row. Periodic edges wrap the global index at load time.
+// Requires Phi_boundary == T_boundary and no corrector guess (otherwise the host falls back to the tiled kernel /
+// the general per-stage kernels).
+//
+// Multi-GPU slabs: `row0` is the global row of local row 0; the launch produces rows [own_y0, own_y1) and reads
+// H rows beyond them, which the slab layout provides as ghost rows.
+#pragma once
+#include "pf_common.cuh"
+#include "pf_fused.cuh"
+
+namespace pf {
+
+constexpr __host__ __device__ int pmod(int a, int m) { return ((a % m) + m) % m; }
+constexpr __host__ __device__ int pow2_at_least(int n) { int p = 1; while(p < n) p *= 2; return p; }
+
+// Geometry of the pipeline for a scheme and a skew.
+template <int SCHEME, int SK>
+struct StreamGeom {
+    static constexpr int NST = SchemeStages<SCHEME>::value;
+    static constexpr int U = SK + 2;                                  // unroll factor = ring size of the register rings and of the exchange ring
+    static constexpr int YR = pow2_at_least(SK * (NST - 1) + 2);     // rows of canon y kept in shared memory
+    static constexpr int FILL = (SK + 1) * (NST - 1);                // first iteration in which every stage is active
+    static constexpr int TAIL = (SK - 1) * (NST - 1);                // iterations after stage 1 has finished
+#ifndef PF_STREAM_PD
+#define PF_STREAM_PD 1
+#endif
+    static constexpr int PD = PF_STREAM_PD;                          // prefetch distance of the y loads, in iterations (1 or 2)
+};
+
+// Forces two values to be computed where this call stands (the compiler may not sink them into a later branch).
+__device__ __forceinline__ void keep_here(double& a, double& b) { asm volatile("" : "+d"(a), "+d"(b)); }
+__device__ __forceinline__ void keep_here(float& a, float& b)   { asm volatile("" : "+f"(a), "+f"(b)); }
+
+// v with the sign bit set when `bit` is 1 (v is +0 in that case: restores a raw -0).
+__device__ __forceinline__ double with_sign(double v, unsigned bit)
+{
+    return __hiloint2double(__double2hiint(v) | (int)(bit << 31), __double2loint(v));
+}
+__device__ __forceinline__ float with_sign(float v, unsigned bit) { return __int_as_float(__float_as_int(v) | (int)(bit << 31)); }
+
+// Per-thread pipeline state. Every array is indexed with compile-time constants only (after unrolling), so it lives
+// in registers and unused slots cost nothing.
+template <typename Real, int SCHEME, int SK>
+struct StreamState {
+    using G = StreamGeom<SCHEME, SK>;
+    Real yF[G::U], yT[G::U];               // canon_zero(y(n)) of rows g1-1, g1, g1+1 (and the retiring g1+2), by row mod U
+    Real cF[G::NST][G::U], cT[G::NST][G::U];   // c[s-1] = input of stage s (s >= 2), by row mod U
+    Real aF[G::NST][SK], aT[G::NST][SK];   // a[s][it mod SK]: what stage s leaves for stage s+1 (RK4: k1+2k2+..; RKM: k1, later k1+4k4)
+    Real bF[G::NST][SK], bT[G::NST][SK];   // RKM: k3, later the error combination
+    Real pF, pT;                           // raw y of row g1 + 2, in flight since the previous iteration (prefetch distance 2)
+    unsigned negmask;                      // raw y was -0: bits (2d, 2d+1) = (Phi, T) of row g1 + 1 - d during an iteration (shifted by 2 every row)
+    Real errF, errT;                       // RKM: running max of the error combination over the cells this thread stored
+};
+
+template <typename Real>
+struct StreamCtx {
+    using V2 = typename Vec2T<Real>::type;
+    V2* ybuf;                          // ring of canon y rows, offset to this thread's slot
+    V2* cbuf;                          // U-deep ring of the stage-input rows of stages 2..NST, offset to this thread's slot
+    size_t lx;                         // clamped / wrapped column for loads
+    size_t out_off;                    // gx - row0*nx: added to row*nx for the stores
+    bool wr_self;                      // this thread publishes its own values (false for the column just outside a non-periodic edge)
+    bool x_lo_edge, x_hi_edge;         // non-periodic domain edge columns: they publish the ghost pair for the column outside
+    bool st_ok;                        // this thread's column is an interior column inside the domain
+    bool edge_cta;                     // block-uniform: some thread of this CTA is a domain edge column
+    int G0;                            // global row of stage 1 in iteration 0
+    int Y0, Y1;                        // rows this CTA produces
+    int ylo, yhi;                      // rows a stage may be evaluated on (domain rows; everything when periodic)
+};
+
+template <typename Real>
+__device__ __forceinline__ void stream_store_pair(typename Vec2T<Real>::type* p, const bool on, const Real vF, const Real vT)
+{
+    typename Vec2T<Real>::type v; v.x = vF; v.y = vT;
+    if(on) *p = v;
+}
+
+// Domain edge columns also publish the ghost pair of boundary_sample into the slot of the column outside.
+template <typename Real>
+__device__ __forceinline__ void stream_store_ghost(const FusedArgs<Real>& a, const StreamCtx<Real>& c, typename Vec2T<Real>::type* p, const Real vF, const Real vT)
+{
+    typename Vec2T<Real>::type g; g.x = ghost_of(vF, a.bc); g.y = ghost_of(vT, a.bc);
+    if(c.x_lo_edge) p[-1] = g;
+    if(c.x_hi_edge) p[+1] = g;
+}
+
+// One stage of one iteration. PH = it mod U, S = stage (1-based). CHECKED: test whether the stage is active in this
+// iteration and apply the y-boundary ghosts; otherwise the caller guarantees both are unnecessary.
+// `old` is the state as it was when the iteration began (the running combinations are handed from stage s to stage
+// s+1 across iterations, so stage s+1 must not see what stage s writes in this one).
+template <typename Real, int SCHEME, bool ANISO, int EW, int SK, bool CHECKED, int PH, int S>
+__device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const StreamCtx<Real>& c,
+                                             const StreamState<Real, SCHEME, SK>& old, StreamState<Real, SCHEME, SK>& st, const int it)
+{
+    using V2 = typename Vec2T<Real>::type;
+    using G = StreamGeom<SCHEME, SK>;
+    constexpr int NST = G::NST, U = G::U, ROWSTRIDE = EW + 2;
+    constexpr int rel = PH - SK * (S - 1);
+    constexpr int jc = pmod(rel, U), jn = pmod(rel + 1, U), js = pmod(rel - 1, U);
+    constexpr int ai = PH % SK;
+    const int row = c.G0 + it - SK * (S - 1);
+    if(CHECKED)
+    {
+        const bool act = row >= c.Y0 - (NST - S) && row < c.Y1 + (NST - S) && row >= c.ylo && row < c.yhi;     // block-uniform
+        if(!act) return;
+    }
+
+    Real CF, CT, NF, NT, SF, ST, y0F, y0T;
+    V2 e, w;
+    const V2* const yrow = c.ybuf + (row & (G::YR - 1)) * ROWSTRIDE;
+    if(S == 1)
+    {
+        CF = st.yF[jc]; CT = st.yT[jc]; NF = st.yF[jn]; NT = st.yT[jn]; SF = st.yF[js]; ST = st.yT[js];
+        e = yrow[1]; w = yrow[-1];
+        y0F = CF; y0T = CT;
+    }
+    else
+    {
+        CF = st.cF[S - 1][jc]; CT = st.cT[S - 1][jc]; NF = st.cF[S - 1][jn]; NT = st.cT[S - 1][jn]; SF = st.cF[S - 1][js]; ST = st.cT[S - 1][js];
+        const V2* const crow = c.cbuf + (pmod(PH - SK, U) * (NST - 1) + (S - 2)) * ROWSTRIDE;     // published SK iterations ago
+        e = crow[1]; w = crow[-1];
+        const V2 y0 = yrow[0];                                              // canon_zero(y) of this row, own column
+        y0F = y0.x; y0T = y0.y;
+    }
+    if(CHECKED && a.bc != PF_BOUNDARY_PERIODIC)
+    {
+        if(row == a.ny_global - 1) { NF = ghost_of(CF, a.bc); NT = ghost_of(CT, a.bc); }
+        if(row == 0)               { SF = ghost_of(CF, a.bc); ST = ghost_of(CT, a.bc); }
+    }
+    Real kF, kT;
+    rhs_cell<Real, ANISO, true, 0>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);
+
+    Real nF = 0, nT = 0;
+    if(SCHEME == SCHEME_EULER)
+    {
+        nF = pf_fma(a.k.dt, kF, CF);                                        // simulation.cu:233-234
+        nT = pf_fma(a.k.dt, kT, CT);
+    }
+    else if(SCHEME == SCHEME_RK4)
+    {
+        if(S == 1)      { st.aF[1][ai] = kF; st.aT[1][ai] = kT;
+                          nF = pf_fma(kF, a.w[0], y0F); nT = pf_fma(kT, a.w[0], y0T); }
+        else if(S == 2) { st.aF[2][ai] = pf_fma((Real) 2, kF, old.aF[1][ai]); st.aT[2][ai] = pf_fma((Real) 2, kT, old.aT[1][ai]);     // k1 + 2*k2 (2*k exact)
+                          nF = pf_fma(kF, a.w[1], y0F); nT = pf_fma(kT, a.w[1], y0T); }
+        else if(S == 3) { st.aF[3][ai] = pf_fma((Real) 2, kF, old.aF[2][ai]); st.aT[3][ai] = pf_fma((Real) 2, kT, old.aT[2][ai]);
+                          nF = pf_fma(kF, a.w[2], y0F); nT = pf_fma(kT, a.w[2], y0T); }
+        else            { kF = old.aF[3][ai] + kF; kT = old.aT[3][ai] + kT; }  // simulation.cu:336-337, finished below with the raw y
+    }
+    else
+    {
+        if(S == 1)      { st.aF[1][ai] = kF; st.aT[1][ai] = kT;                                                         // k1
+                          nF = pf_fma(kF, a.w[0], y0F); nT = pf_fma(kT, a.w[0], y0T); }                                 // y + tau/3 k1
+        else if(S == 2) { st.aF[2][ai] = old.aF[1][ai]; st.aT[2][ai] = old.aT[1][ai];
+                          nF = pf_fma(kF, a.w[1], pf_fma(old.aF[1][ai], a.w[1], y0F));                                  // y + tau/6 k1 + tau/6 k2
+                          nT = pf_fma(kT, a.w[1], pf_fma(old.aT[1][ai], a.w[1], y0T)); }
+        else if(S == 3) { st.aF[3][ai] = old.aF[2][ai]; st.aT[3][ai] = old.aT[2][ai];
+                          st.bF[3][ai] = kF; st.bT[3][ai] = kT;                                                         // k3
+                          nF = pf_fma(kF, a.w[3], pf_fma(old.aF[2][ai], a.w[2], y0F));                                  // y + tau/8 k1 + 3tau/8 k3
+                          nT = pf_fma(kT, a.w[3], pf_fma(old.aT[2][ai], a.w[2], y0T)); }
+        else if(S == 4) { nF = pf_fma(kF, a.w[6], pf_fma(old.bF[3][ai], a.w[5], pf_fma(old.aF[3][ai], a.w[4], y0F)));   // y + tau/2 k1 - 3tau/2 k3 + 2tau k4
+                          nT = pf_fma(kT, a.w[6], pf_fma(old.bT[3][ai], a.w[5], pf_fma(old.aT[3][ai], a.w[4], y0T)));
+                          // error combination so far: 0.2*k1 - 0.9*k3 + 0.8*k4 (simulation.cu:428); nvcc rounds 0.9*k3 and fuses the rest
+                          st.bF[4][ai] = pf_fma((Real) 0.8, kF, pf_fma((Real) 0.2, old.aF[3][ai], -((Real) 0.9 * old.bF[3][ai])));
+                          st.bT[4][ai] = pf_fma((Real) 0.8, kT, pf_fma((Real) 0.2, old.aT[3][ai], -((Real) 0.9 * old.bT[3][ai])));
+                          st.aF[4][ai] = pf_fma((Real) 4, kF, old.aF[3][ai]); st.aT[4][ai] = pf_fma((Real) 4, kT, old.aT[3][ai]); }   // k1 + 4*k4 (exact product)
+        else            { Real eF = pf_fma(-(Real) 0.1, kF, old.bF[4][ai]);
+                          Real eT = pf_fma(-(Real) 0.1, kT, old.bT[4][ai]);
+                          eF = eF >= 0 ? eF : -eF;
+                          eT = eT >= 0 ? eT : -eT;
+                          if(c.st_ok) { st.errF = eF > st.errF ? eF : st.errF; st.errT = eT > st.errT ? eT : st.errT; }
+                          kF = old.aF[4][ai] + kF; kT = old.aT[4][ai] + kT; }                                           // simulation.cu:472, finished below
+    }
+
+    if(S < NST)
+    {
+        st.cF[S][jc] = nF; st.cT[S][jc] = nT;
+        stream_store_pair<Real>(c.cbuf + (PH * (NST - 1) + (S - 1)) * ROWSTRIDE, c.wr_self, nF, nT);
+    }
+    else
+    {
+        if(SCHEME != SCHEME_EULER)
+        {
+            // y(n+1) = y + w*(combination) with the RAW y (a -0 stays -0 here, as in the reference's final combine)
+            constexpr int d = 1 + SK * (NST - 1);
+            const Real rawF = with_sign(y0F, (st.negmask >> (2 * d)) & 1u);
+            const Real rawT = with_sign(y0T, (st.negmask >> (2 * d + 1)) & 1u);
+            const Real wl = SCHEME == SCHEME_RK4 ? a.w[3] : a.w[7];
+            nF = pf_fma(wl, kF, rawF);
+            nT = pf_fma(wl, kT, rawT);
+        }
+        // keep the last stage in the straight-line code of the row (the halo threads compute it too, only the store is predicated)
+        keep_here(nF, nT);
+        if(c.st_ok)
+        {
+            const size_t idx = (size_t) row * (size_t) a.nx + c.out_off;
+            a.out_F[idx] = nF;
+            a.out_U[idx] = nT;
+        }
+    }
+}
+
+template <typename Real, int SCHEME, bool ANISO, int EW, int SK, bool CHECKED, int PH, int S>
+struct StreamStages {
+    static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c,
+                                               const StreamState<Real, SCHEME, SK>& old, StreamState<Real, SCHEME, SK>& st, const int it)
+    {
+        stream_stage<Real, SCHEME, ANISO, EW, SK, CHECKED, PH, S>(a, c, old, st, it);
+        if constexpr (S < SchemeStages<SCHEME>::value)
+            StreamStages<Real, SCHEME, ANISO, EW, SK, CHECKED, PH, S + 1>::run(a, c, old, st, it);
+    }
+};
+
+// Local memory row of global row g: wrapped (single GPU, periodic) or clamped into the rows that exist locally and
+// in the domain, so that loads of rows that only feed garbage stay inside the allocation.
+template <typename Real>
+__device__ __forceinline__ size_t stream_mem_row(const FusedArgs<Real>& a, int g, const int rlo, const int rhi)
+{
+    if(a.wrap_y) { while(g < 0) g += a.ny_global; while(g >= a.ny_global) g -= a.ny_global; }
+    g = g < rlo ? rlo : (g > rhi ? rhi : g);
+    return (size_t)(g - a.row0);
+}
+
+// One row of the march. PH = it mod U.
+template <typename Real, int SCHEME, bool ANISO, int EW, int SK, bool CHECKED, int PH>
+__device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME, SK>& st,
+                                                 const int it, const int rlo, const int rhi)
+{
+    using V2 = typename Vec2T<Real>::type;
+    using G = StreamGeom<SCHEME, SK>;
+    constexpr int NST = G::NST, U = G::U, ROWSTRIDE = EW + 2;
+    constexpr int j1 = pmod(PH + 1, U), j2 = pmod(PH + 2, U);
+    const int g1 = c.G0 + it;
+    // 1. prefetch the raw y: PD = 1: row g1 + 2, retired at the end of this iteration; PD = 2: row g1 + 3, retired at the
+    //    end of the NEXT iteration (two full iterations to arrive, two more registers pairs in flight)
+    const size_t ro = (CHECKED ? stream_mem_row(a, g1 + 1 + G::PD, rlo, rhi) : (size_t)(g1 + 1 + G::PD - a.row0)) * (size_t) a.nx + c.lx;
+    const Real tF = a.F[ro], tT = a.U[ro];
+    // 2. publish y of row g1 + 1: the E/W neighbours of stage 1 in the NEXT iteration, and the y the later stages re-read
+    V2* const ypub = c.ybuf + ((g1 + 1) & (G::YR - 1)) * ROWSTRIDE;
+    stream_store_pair<Real>(ypub, c.wr_self, st.yF[j1], st.yT[j1]);
+    // 3. all stages
+    {
+        const StreamState<Real, SCHEME, SK> old = st;
+        StreamStages<Real, SCHEME, ANISO, EW, SK, CHECKED, PH, 1>::run(a, c, old, st, it);
+    }
+    // 3b. CTAs that hold a non-periodic domain edge column: the ghost pairs of everything published in this row
+    if(c.edge_cta)
+    {
+        stream_store_ghost<Real>(a, c, ypub, st.yF[j1], st.yT[j1]);
+        #pragma unroll
+        for(int S = 1; S < NST; S++)
+            stream_store_ghost<Real>(a, c, c.cbuf + (PH * (NST - 1) + (S - 1)) * ROWSTRIDE,
+                                     st.cF[S][pmod(PH - SK * (S - 1), U)], st.cT[S][pmod(PH - SK * (S - 1), U)]);
+    }
+    // 4. retire the prefetch of row g1 + 2
+    {
+        const Real rF = G::PD == 2 ? st.pF : tF, rT = G::PD == 2 ? st.pT : tT;
+        st.yF[j2] = canon_zero(rF); st.yT[j2] = canon_zero(rT);
+        if(SCHEME != SCHEME_EULER)
+            st.negmask = (st.negmask << 2) | (unsigned) is_negzero(rF) | ((unsigned) is_negzero(rT) << 1);
+        if(G::PD == 2) { st.pF = tF; st.pT = tT; }
+    }
+    // 5. one barrier per row: this iteration's writes become visible, the slots they will overwrite next have been read
+    __syncthreads();
+}
+
+template <typename Real, int SCHEME, bool ANISO, int EW, int SK, bool CHECKED, int PH>
+struct StreamIters {
+    static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME, SK>& st,
+                                               const int it0, const int rlo, const int rhi)
+    {
+        stream_iteration<Real, SCHEME, ANISO, EW, SK, CHECKED, PH>(a, c, st, it0 + PH, rlo, rhi);
+        if constexpr (PH + 1 < StreamGeom<SCHEME, SK>::U)
+            StreamIters<Real, SCHEME, ANISO, EW, SK, CHECKED, PH + 1>::run(a, c, st, it0, rlo, rhi);
+    }
+};
+
+template <typename Real, int SCHEME, int WARPS, int SK>
+constexpr size_t stream_smem_bytes()
+{
+    using G = StreamGeom<SCHEME, SK>;
+    return sizeof(typename Vec2T<Real>::type) * (size_t)(G::YR + G::U * (G::NST - 1)) * (32 * WARPS + 2);
+}
+
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB, int SK>
+__global__ void __launch_bounds__(32 * WARPS, MINB)
+k_stream_step(const FusedArgs<Real> a)
+{
+    using V2 = typename Vec2T<Real>::type;
+    using G = StreamGeom<SCHEME, SK>;
+    constexpr int NST = G::NST, U = G::U;
+    constexpr int H = NST, EW = 32 * WARPS, EWI = EW - 2 * H, ROWSTRIDE = EW + 2;
+    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
+    V2* const smem = reinterpret_cast<V2*>(pf_smem_raw);
+
+    const int nx = a.nx, NY = a.ny_global;
+    const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
+
+    StreamCtx<Real> c;
+    const int cx = threadIdx.x;
+    const int strip_x0 = (int) blockIdx.x * EWI;
+    const int gx = strip_x0 - H + cx;
+    if(periodic) { int lx = gx % nx; if(lx < 0) lx += nx; c.lx = (size_t) lx; }
+    else         c.lx = (size_t)(gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx));
+    c.x_lo_edge = !periodic && gx == 0;
+    c.x_hi_edge = !periodic && gx == nx - 1;
+    c.wr_self = periodic || (gx != -1 && gx != nx);
+    c.st_ok = cx >= H && cx < EW - H && gx < nx;
+    c.edge_cta = !periodic && (strip_x0 - H <= 0 || strip_x0 - H + EW >= nx);
+    c.out_off = (size_t)((long long) gx - (long long) a.row0 * (long long) nx);
+    c.Y0 = a.own_y0 + (int) blockIdx.y * a.chunk;
+    c.Y1 = min(c.Y0 + a.chunk, a.own_y1);
+    c.G0 = c.Y0 - (NST - 1);
+    c.ylo = periodic ? INT_MIN : 0;
+    c.yhi = periodic ? INT_MAX : NY;
+    c.ybuf = smem + cx + 1;
+    c.cbuf = smem + G::YR * ROWSTRIDE + cx + 1;
+    const int n_it = (c.Y1 - c.Y0) + (SK + 1) * (NST - 1);
+    // rows that exist both locally and in the domain (loads are clamped into them)
+    const int rlo = periodic ? a.row0 : max(a.row0, 0);
+    const int rhi = (periodic ? a.row0 + a.rows_local : min(a.row0 + a.rows_local, NY)) - 1;
+
+    StreamState<Real, SCHEME, SK> st;
+    #pragma unroll
+    for(int j = 0; j < U; j++)
+    {
+        st.yF[j] = st.yT[j] = 0;
+        #pragma unroll
+        for(int s = 0; s < NST; s++) { st.cF[s][j] = 0; st.cT[s][j] = 0; }
+    }
+    #pragma unroll
+    for(int s = 0; s < NST; s++)
+    {
+        #pragma unroll
+        for(int j = 0; j < SK; j++) { st.aF[s][j] = st.aT[s][j] = 0; st.bF[s][j] = st.bT[s][j] = 0; }
+    }
+    st.negmask = 0; st.errF = 0; st.errT = 0;
+
+    // zero the rings (pads included), then preload y rows G0-1, G0, G0+1
+    for(int i = threadIdx.x; i < (G::YR + U * (NST - 1)) * ROWSTRIDE; i += EW) { V2 z; z.x = 0; z.y = 0; smem[i] = z; }
+    #pragma unroll
+    for(int d = -1; d <= 1; d++)
+    {
+        const size_t ro = stream_mem_row(a, c.G0 + d, rlo, rhi) * (size_t) nx + c.lx;
+        const Real f = a.F[ro], u = a.U[ro];
+        const int j = d < 0 ? U - 1 : d;
+        st.yF[j] = canon_zero(f); st.yT[j] = canon_zero(u);
+        st.negmask = (st.negmask << 2) | (unsigned) is_negzero(f) | ((unsigned) is_negzero(u) << 1);
+    }
+    {
+        const size_t ro = stream_mem_row(a, c.G0 + 2, rlo, rhi) * (size_t) nx + c.lx;
+        st.pF = a.F[ro]; st.pT = a.U[ro];
+    }
+    __syncthreads();
+    {
+        V2* const ypub = c.ybuf + (c.G0 & (G::YR - 1)) * ROWSTRIDE;
+        stream_store_pair<Real>(ypub, c.wr_self, st.yF[0], st.yT[0]);
+        if(c.edge_cta) stream_store_ghost<Real>(a, c, ypub, st.yF[0], st.yT[0]);
+    }
+    __syncthreads();
+
+    // Iterations run in groups of U. A group takes the straight-line form when, in all of its iterations, every stage
+    // is active, no stage row is a non-periodic domain edge row (or outside the domain), and the prefetched row
+    // needs neither clamping nor wrapping.
+    int lo_it = max(G::FILL, rlo - 1 - G::PD - c.G0);
+    int hi_it = min((c.Y1 - c.Y0) + 2 * NST - 2, rhi - G::PD - c.G0);
+    if(!periodic) { lo_it = max(lo_it, 1 - c.G0 + SK * (NST - 1)); hi_it = min(hi_it, NY - 1 - c.G0); }
+    for(int it0 = 0; it0 < n_it; it0 += U)
+    {
+        if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, SK, false, 0>::run(a, c, st, it0, rlo, rhi);
+        else                                 StreamIters<Real, SCHEME, ANISO, EW, SK, true, 0>::run(a, c, st, it0, rlo, rhi);
+    }
+
+    if(SCHEME == SCHEME_RKM)
+    {
+        const Real eF = warp_max(st.errF), eT = warp_max(st.errT);
+        if((threadIdx.x & 31) == 0)
+        {
+            if(eF > 0) atomic_max_nonneg(a.err_bits + 0, eF);
+            if(eT > 0) atomic_max_nonneg(a.err_bits + 1, eT);
+        }
+    }
+}
+
+} // namespace pf
