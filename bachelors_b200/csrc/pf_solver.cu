@@ -15,6 +15,7 @@
 #include "../../include/pf_solver.h"
 #include "pf_common.cuh"
 #include "pf_fused.cuh"
+#include "pf_stream.cuh"
 #include "pf_general.cuh"
 
 using namespace pf;
@@ -48,6 +49,7 @@ struct pf_solver {
     int last_num_steps = 0;                 // simulation.cu:936
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
+    unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
     int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
@@ -375,7 +377,7 @@ static int launch_fused_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bi
 }
 
 template <typename Real>
-static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
+static int launch_tiled(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
 {
     const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
     switch(scheme * 2 + (aniso ? 1 : 0))
@@ -386,6 +388,78 @@ static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
         case 3: return launch_fused_inst<Real, SCHEME_RK4, true>(s, a, base);
         case 4: return launch_fused_inst<Real, SCHEME_RKM, false>(s, a, base);
         default: return launch_fused_inst<Real, SCHEME_RKM, true>(s, a, base);
+    }
+}
+
+// ---- streaming kernel (pf_stream.cuh): launch geometry -------------------------------------------------
+// CTA = 4 warps (128 columns, 128 - 2*NST of them interior). Resident CTAs per SM by register budget:
+// Euler 8 (<= 64 registers), the multi-stage schemes 4 (<= 128 registers); skew 1 (measured faster than skew 2).
+enum { STREAM_WARPS = 4, STREAM_SK = 1 };
+template <int SCHEME, bool ANISO> struct StreamOcc { static constexpr int MINB = SCHEME == SCHEME_EULER ? (ANISO ? 6 : 8) : 4; };
+
+// Number of row chunks: every CTA marches down `chunk` rows plus a pipeline fill of ~(SK+1)(NST-1) rows, so few long
+// chunks waste the least work, but the grid should fill the machine's resident-CTA slots in whole waves. Cost model
+// (fitted to kbench runs on B200): a wave costs iterations x (a + b x resident CTAs per SM).
+static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
+{
+    const long long slots = (long long) sm_count * minb;
+    double best = 1e300; int best_n = 1;
+    const int max_n = std::max(1, rows / 4);
+    for(int n = 1; n <= max_n; n++)
+    {
+        const int chunk = (rows + n - 1) / n;
+        const int nch = (rows + chunk - 1) / chunk;
+        const long long ctas = (long long) strips * nch;
+        const long long full = ctas / slots, rest = ctas % slots;
+        const double its = chunk + fill + 3.0;                       // the checked first/last groups run slower
+        const double occ_rest = std::min<double>(minb, std::ceil((double) rest / sm_count));
+        const double cost = its * (full * (0.6 + 0.145 * minb) + (rest ? 0.6 + 0.145 * occ_rest : 0.0));
+        if(cost < best) { best = cost; best_n = nch; }
+    }
+    return best_n;
+}
+
+template <typename Real, int SCHEME, bool ANISO>
+static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
+{
+    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, SK = STREAM_SK, MINB = StreamOcc<SCHEME, ANISO>::MINB;
+    constexpr int EWI = 32 * W - 2 * NST;
+    static_assert(EWI > 0, "strip too narrow for the stage count");
+    auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB, SK>;
+    const size_t smem = stream_smem_bytes<Real, SCHEME, W, SK>();
+    if(!(s->stream_attr_done & (1u << inst_bit)))
+    {
+        PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        s->stream_attr_done |= 1u << inst_bit;
+    }
+    const int own_rows = a.own_y1 - a.own_y0;
+    if(own_rows <= 0) return PF_OK;
+    const int strips = (a.nx + EWI - 1) / EWI;
+    const int nch = stream_chunks(s->sm_count, MINB, strips, own_rows, (SK + 1) * (NST - 1));
+    a.chunk = (own_rows + nch - 1) / nch;
+    cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
+    dim3 grid((unsigned) strips, (unsigned)((own_rows + a.chunk - 1) / a.chunk));
+    kern<<<grid, 32 * W, smem, stream>>>(a);
+    PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+// One launch = one whole time step (or one Merson attempt). The streaming kernel is the product path; a step with the
+// corrector guess (a different right-hand side, simulation.cu:221-225) takes the tiled kernel.
+template <typename Real>
+static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
+{
+    if(a.k.do_corrector_guess) return launch_tiled<Real>(s, scheme, aniso, a);
+    const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
+    switch(scheme * 2 + (aniso ? 1 : 0))
+    {
+        case 0: return launch_stream_inst<Real, SCHEME_EULER, false>(s, a, base);
+        case 1: return launch_stream_inst<Real, SCHEME_EULER, true>(s, a, base);
+        case 2: return launch_stream_inst<Real, SCHEME_RK4, false>(s, a, base);
+        case 3: return launch_stream_inst<Real, SCHEME_RK4, true>(s, a, base);
+        case 4: return launch_stream_inst<Real, SCHEME_RKM, false>(s, a, base);
+        default: return launch_stream_inst<Real, SCHEME_RKM, true>(s, a, base);
     }
 }
 

@@ -162,13 +162,13 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
         if(row == 0)               { SF = ghost_of(CF, a.bc); ST = ghost_of(CT, a.bc); }
     }
     Real kF, kT;
-    rhs_cell<Real, ANISO, true, 0>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);
+    rhs_cell_lean<Real, ANISO>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);       // kT without the reference's "+ fu"
 
     Real nF = 0, nT = 0;
     if(SCHEME == SCHEME_EULER)
     {
         nF = pf_fma(a.k.dt, kF, CF);                                        // simulation.cu:233-234
-        nT = pf_fma(a.k.dt, kT, CT);
+        nT = pf_fma(a.k.dt, kT, CT);                                        // C_T is never -0, so the missing "+ fu" cannot show
     }
     else if(SCHEME == SCHEME_RK4)
     {
@@ -219,6 +219,10 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
             const Real rawF = with_sign(y0F, (st.negmask >> (2 * d)) & 1u);
             const Real rawT = with_sign(y0T, (st.negmask >> (2 * d + 1)) & 1u);
             const Real wl = SCHEME == SCHEME_RK4 ? a.w[3] : a.w[7];
+            // The reference adds fu = 0 to every k_T, which turns a -0 into +0 and changes nothing else. Stage inputs are
+            // insensitive to that sign (they add k*w to a canonical y, which is never -0), error norms take |.|, and a
+            // combination of k's is -0 only if all of them are: adding 0 once, here, gives the same bits.
+            kT = kT + a.k.fu;
             nF = pf_fma(wl, kF, rawF);
             nT = pf_fma(wl, kT, rawT);
         }
