@@ -86,7 +86,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._halt.wait(0.02)
+            self._halt.wait(0.004)
 
     def finish(self):
         self._halt.set()
@@ -299,7 +299,7 @@ def run_cuda_arm(args):
     glups = cells * args.steps / (ms * 1e-3) / 1e9
     rs = 8 if dtype == PF_F64 else 4
     peak, peak_src = load_peaks()
-    # dominant kernel: the fused step kernel, one launch per step (adaptive: one per attempt) producing this rank's rows
+    # dominant kernel: the streaming step kernel (pf_stream.cuh), one launch per step (adaptive: one per attempt) producing this rank's rows
     launches_per_step = launches / args.steps
     alg_bytes_per_launch = 4 * rs * (cells / world)                    # read Phi, T + write Phi', T' 
     avg_launch_s = (ms * 1e-3) / max(attempts if args.solver == "explicit-rk4-adaptive" else args.steps, 1)
@@ -325,7 +325,7 @@ def run_cuda_arm(args):
                                  % (4 * rs * cells / world / 1e6)),
                    "halo_overlap": (not args.no_overlap) if world > 1 else None},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "k_fused_step", "peak_source": peak_src,
+                     "kernel": "k_stream_step", "peak_source": peak_src,
                      "algorithmic_bytes_per_cell_step": 4 * rs, "launches_per_step": launches_per_step},
         "e2e": {"value": e2e_glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                 "steps": e2e_steps, "what": "pf_upload(Phi,T) from pinned host + pf_step + pf_download(Phi,T) every step"},
@@ -376,8 +376,8 @@ def same_box_reference(cfg, dtype, args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--solver", default="explicit-rk4", choices=[k for k in SOLVER_NAMES if k not in ("none", "exact", "semi-implicit")])
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
