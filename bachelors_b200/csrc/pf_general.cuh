@@ -138,13 +138,9 @@ __global__ void k_debug_values(const Real* __restrict__ F, const Real* __restric
 // The prepare kernel: right-hand side b_F and per-cell factor s of A_Phi. Reference simulation.cu:800-834 (guess)
 // and :838-870 (no guess; note the DIVISION by 2*dx / 2*dy there).
 template <typename Real, bool ANISO>
-__global__ void __launch_bounds__(256)
-k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __restrict__ b_F, Real* __restrict__ factor_out,
-             int nx, int ny, int F_bound, int U_bound, KConsts<Real> k)
+__device__ __forceinline__ void si_prepare_cell(const Real* __restrict__ F, const Real* __restrict__ U, int x, int y,
+                                                int nx, int ny, int F_bound, int U_bound, const KConsts<Real>& k, Real& right_out, Real& factor_out)
 {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    if(x >= nx || y >= ny) return;
     const size_t i = (size_t) x + (size_t) y * (size_t) nx;
     const Real C_Phi = F[i];
     const Real E_Phi = bsample(F, x + 1, y, nx, ny, F_bound);
@@ -186,6 +182,20 @@ k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __res
         right = pf_fma(k.dt, inner, C_Phi);
         factor = k.gamma * k1;
     }
+    right_out = right; factor_out = factor;
+}
+
+template <typename Real, bool ANISO>
+__global__ void __launch_bounds__(256)
+k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __restrict__ b_F, Real* __restrict__ factor_out,
+             int nx, int ny, int F_bound, int U_bound, KConsts<Real> k)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    if(x >= nx || y >= ny) return;
+    const size_t i = (size_t) x + (size_t) y * (size_t) nx;
+    Real right, factor;
+    si_prepare_cell<Real, ANISO>(F, U, x, y, nx, ny, F_bound, U_bound, k, right, factor);
     factor_out[i] = factor;
     b_F[i] = right;
 }
@@ -212,8 +222,9 @@ struct CgMatrix {
     int nx, ny, boundary;
 };
 
+// (A*vec)(x, y); `sc` is the per-cell factor of A_Phi at this cell (ignored for A_T).
 template <typename Real>
-__device__ __forceinline__ Real cg_apply(const CgMatrix<Real>& A, const Real* __restrict__ vec, int x, int y)
+__device__ __forceinline__ Real cg_apply_sc(const CgMatrix<Real>& A, const Real* __restrict__ vec, int x, int y, Real sc)
 {
     const int nx = A.nx, ny = A.ny;
     const size_t i = (size_t) x + (size_t) y * (size_t) nx;
@@ -225,7 +236,6 @@ __device__ __forceinline__ Real cg_apply(const CgMatrix<Real>& A, const Real* __
     Real val;
     if(A.which == 0)
     {
-        const Real sc = A.factor[i];
         const Real X = A.X * sc, Y = A.Y * sc;
         const Real Cc = pf_fma(A.C_minus_one, sc, (Real) 1);
         val = c * Cc;
@@ -237,6 +247,12 @@ __device__ __forceinline__ Real cg_apply(const CgMatrix<Real>& A, const Real* __
         val = pf_fma(e, A.R, val); val = pf_fma(w, A.Lc, val); val = pf_fma(n, A.Uc, val); val = pf_fma(s, A.D, val);
     }
     return val;
+}
+
+template <typename Real>
+__device__ __forceinline__ Real cg_apply(const CgMatrix<Real>& A, const Real* __restrict__ vec, int x, int y)
+{
+    return cg_apply_sc(A, vec, x, y, A.which == 0 ? A.factor[(size_t) x + (size_t) y * (size_t) A.nx] : (Real) 0);
 }
 
 // Device-resident CG control block: no host round trip per iteration (the reference blocks on a D2H copy

@@ -17,6 +17,7 @@
 #include "pf_fused.cuh"
 #include "pf_stream.cuh"
 #include "pf_general.cuh"
+#include "pf_si_coop.cuh"
 
 using namespace pf;
 
@@ -50,6 +51,8 @@ struct pf_solver {
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
+    int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
+    bool force_per_kernel_cg = false;       // test hook (PF_SI_PER_KERNEL=1): take the per-kernel CG path
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
     int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
@@ -159,6 +162,7 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
         fail(s, e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA); } } while(0)
     PF_CREATE_CUDA(cudaSetDevice(device));
     PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
+    { const char* e = getenv("PF_SI_PER_KERNEL"); s->force_per_kernel_cg = e && e[0] == '1'; }   // test hook: see tests/test_gpu_parity.py
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
@@ -764,11 +768,64 @@ static CgMatrix<Real> make_matrix(const pf_params& p, int which, const Real* fac
     return A;
 }
 
+// The whole step as ONE cooperative launch (pf_si_coop.cuh) when its grid can be co-resident; *used = 0 otherwise.
+template <typename Real, bool ANISO>
+static int semi_implicit_step_coop_inst(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU, int* used)
+{
+    *used = 0;
+    const int slot = (sizeof(Real) == 8 ? 0 : 2) + (ANISO ? 1 : 0);
+    auto kern = k_si_step_coop<Real, ANISO>;
+    if(s->coop_blocks_per_sm[slot] < 0)
+    {
+        int coop = 0, per_sm = 0;
+        PF_CUDA(s, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, s->device));
+        if(coop) PF_CUDA(s, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, CG_THREADS, 0));
+        s->coop_blocks_per_sm[slot] = coop ? per_sm : 0;
+    }
+    const int blocks = cg_blocks(s, s->nx, s->ny);
+    if(s->force_per_kernel_cg || (long long) s->coop_blocks_per_sm[slot] * s->sm_count < blocks) return PF_OK;
+
+    void* q[4];
+    for(int i = 0; i < 4; i++) if(int rc = get_scratch(s, 4 + i, &q[i])) return rc;     // the per-kernel path's factor, r, p, Ap slots
+    Real* P = (Real*) s->partials;
+    SiCoopArgs<Real> a; memset(&a, 0, sizeof a);
+    a.F = F; a.U = U; a.U_base = U_base; a.nF = nF; a.nU = nU;
+    a.factor = (Real*) q[0]; a.r = (Real*) q[1]; a.p = (Real*) q[2]; a.Ap = (Real*) q[3];
+    a.rr0 = P; a.rr1 = P + CG_MAX_BLOCKS; a.pAp = P + 2 * CG_MAX_BLOCKS;
+    a.st = s->d_cg;
+    a.A_F = make_matrix<Real>(p, 0, a.factor);
+    a.A_U = make_matrix<Real>(p, 1, nullptr);
+    a.k = make_consts<Real>(p);
+    a.nx = s->nx; a.ny = s->ny; a.F_bound = p.Phi_boundary; a.U_bound = p.T_boundary;
+    const size_t N = s->field_elems();
+    a.sst_F = (Real) p.Phi_tolerance * (Real) p.Phi_tolerance * (Real)(int) N;         // simulation.cu:608
+    a.sst_U = (Real) p.T_tolerance * (Real) p.T_tolerance * (Real)(int) N;
+    a.max_F = p.Phi_max_iters; a.max_U = p.T_max_iters;
+    a.L = (Real) p.L; a.dt_omg = (Real) p.dt * (1 - (Real) p.gamma);
+    void* args[] = {&a};
+    PF_CUDA(s, cudaLaunchCooperativeKernel((const void*) kern, dim3((unsigned) blocks), dim3(CG_THREADS), args, 0, s->stream));
+    PF_LAUNCH_CHECK(s);
+    *used = 1;
+    return PF_OK;
+}
+
+template <typename Real>
+static int semi_implicit_step_coop(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU, int* used)
+{
+    if(p.S != 0) return semi_implicit_step_coop_inst<Real, true>(s, p, F, U, U_base, nF, nU, used);
+    return semi_implicit_step_coop_inst<Real, false>(s, p, F, U, U_base, nF, nU, used);
+}
+
 // semi_implicit_solver_step_based: reference simulation.cu:732-926 (without the do_debug back-substitution).
 template <typename Real>
 static int semi_implicit_step_based(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU)
 {
     if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "the semi-implicit solver is single-GPU only in this version");
+    {
+        int used = 0;
+        if(int rc = semi_implicit_step_coop<Real>(s, p, F, U, U_base, nF, nU, &used)) return rc;
+        if(used) return PF_OK;
+    }
     void* q[6];
     for(int i = 0; i < 6; i++) if(int rc = get_scratch(s, 2 + i, &q[i])) return rc;     // slots 0,1 are the corrector's temporaries
     Real *b_F = (Real*) q[0], *b_U = (Real*) q[1], *aniso = (Real*) q[2], *r = (Real*) q[3], *pv = (Real*) q[4], *Ap = (Real*) q[5];

@@ -172,7 +172,14 @@ class SlabRunner:
         elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE:
             dt = self._step_adaptive(p, F, U, nF, nU)
         else:
-            raise S.PfError(-5, "SlabRunner: the semi-implicit solver is single-GPU only in this version")
+            if self.world > 1:
+                raise S.PfError(-5, "SlabRunner: the semi-implicit solver is single-GPU only in this version")
+            # one sim_step-shaped call: returns after the device finished (the CG iteration counts come back with it)
+            info = pf_step_info()
+            s._ck(L.pf_step(s._h, C.byref(p), F, U, nF, nU, C.byref(info)))
+            dt = info.dt_advanced
+            self.last_attempts = 1
+            self.last_cg_iters = (info.Phi_iters, info.T_iters)
         self.F, self.nF = self.nF, self.F
         self.U, self.nU = self.nU, self.U
         self.time += dt

@@ -107,9 +107,10 @@ def physical_gpu_index(local):
 
 def workload(args, world):
     """-> (cfg, description). The config file supplies every parameter; for N > 1 only the grid is widened."""
-    cfg = read_config(os.path.join(ROOT, "benchmark_configs", f"config_{args.solver}_2048.ini"))
+    size = args.size or (1024 if args.solver == "semi-implicit" else 2048)      # BASELINE.json configs: semi-implicit is quoted at 1024^2
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", f"config_{args.solver}_{size}.ini"))
     if world == 1 and not args.wide:
-        return cfg, f"config_{args.solver}_2048.ini ({args.dtype})"
+        return cfg, f"config_{args.solver}_{size}.ini ({args.dtype})"
     p = cfg.params
     dx = p.L0 / p.nx
     p.nx, p.ny = WIDE_NX, PER_GPU_ROWS * world
@@ -199,9 +200,11 @@ def time_device_steps(runner, torch, steps, world, dist):
     torch.cuda.synchronize()
     e0.record(runner.main)
     t_adv, attempts = 0.0, 0
+    runner.cg_iters_total = 0
     for _ in range(steps):
         t_adv += runner.step()
         attempts += runner.last_attempts
+        runner.cg_iters_total += sum(getattr(runner, "last_cg_iters", (0, 0)))
     # the step's tail may live on the aux / comm streams: make main wait for them before the closing event
     runner.main.wait_event(runner.ev_aux)
     runner.main.wait_event(runner.ev_halo)
@@ -304,6 +307,14 @@ def run_cuda_arm(args):
     alg_bytes_per_launch = 4 * rs * (cells / world)                    # read Phi, T + write Phi', T' 
     avg_launch_s = (ms * 1e-3) / max(attempts if args.solver == "explicit-rk4-adaptive" else args.steps, 1)
     achieved = alg_bytes_per_launch / avg_launch_s / 1e9
+    kernel_name, alg_per_cell = "k_stream_step", 4 * rs
+    if args.solver == "semi-implicit":
+        # 4 s for prepare / b_T plus >= 10 s per CG iteration (SpMV 2-3, x/r update 6, p update 3 field passes);
+        # the "launch" of the roofline is the whole step (prepare + both solves)
+        cg_per_step = runner.cg_iters_total / max(args.steps, 1)
+        alg_per_cell = (4 + 10 * cg_per_step) * rs
+        achieved = alg_per_cell * cells / (ms * 1e-3 / args.steps) / 1e9
+        kernel_name = "k_si_prepare + k_cg_spmv/update/pupdate (whole step)"
     traffic = load_traffic(args.solver, args.dtype) if world == 1 and not args.wide else None
 
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
@@ -325,8 +336,8 @@ def run_cuda_arm(args):
                                  % (4 * rs * cells / world / 1e6)),
                    "halo_overlap": (not args.no_overlap) if world > 1 else None},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "k_stream_step", "peak_source": peak_src,
-                     "algorithmic_bytes_per_cell_step": 4 * rs, "launches_per_step": launches_per_step},
+                     "kernel": kernel_name, "peak_source": peak_src,
+                     "algorithmic_bytes_per_cell_step": alg_per_cell, "launches_per_step": launches_per_step},
         "e2e": {"value": e2e_glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
                 "steps": e2e_steps, "what": "pf_upload(Phi,T) from pinned host + pf_step + pf_download(Phi,T) every step"},
         "gpu_launches": tot_launches,
@@ -335,6 +346,8 @@ def run_cuda_arm(args):
     }
     if args.solver == "explicit-rk4-adaptive":
         line["attempts_per_step"] = attempts / args.steps
+    if args.solver == "semi-implicit":
+        line["cg_iterations_per_step"] = runner.cg_iters_total / args.steps
 
     if rank == 0 and world == 1 and not args.no_cpu:
         v, cores, sample = cpu_port_rate(cfg, dtype, budget_s=args.cpu_budget, max_steps=40, w=None if not args.wide else 2048)
@@ -379,8 +392,9 @@ def main():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--solver", default="explicit-rk4", choices=[k for k in SOLVER_NAMES if k not in ("none", "exact", "semi-implicit")])
+    ap.add_argument("--solver", default="explicit-rk4", choices=[k for k in SOLVER_NAMES if k not in ("none", "exact")])
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--size", type=int, default=0, help="N = 1: grid size of the benchmark config (128 ... 2048; default 2048, semi-implicit 1024)")
     ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
     ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
     ap.add_argument("--no-cpu", action="store_true")

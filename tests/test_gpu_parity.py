@@ -409,6 +409,39 @@ def test_semi_implicit_1024_iteration_counts():
     assert rel_l2(gF, oF) <= 1e-10
 
 
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("variant", ["neumann", "periodic_aniso", "dirichlet_theta_half", "corrector_loop"])
+def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, dtype, monkeypatch):
+    """The one-launch cooperative step (pf_si_coop.cuh) and the per-kernel CG path (PF_SI_PER_KERNEL=1, read at pf_create) share
+    decomposition, arithmetic and summation trees: fields, iteration counts and residuals must agree bit for bit."""
+    kw = dict(neumann=dict(),
+              periodic_aniso=dict(Phi_boundary="periodic", T_boundary="periodic", S=0.3),
+              dirichlet_theta_half=dict(Phi_boundary="dirichlet", T_boundary="dirichlet", gamma=0.5, do_corrector_guess=1),
+              corrector_loop=dict(do_corrector_loop=1, corrector_max_iters=2))[variant]
+    nx, ny = 300, 171
+    p = default_params(solver="semi-implicit", nx=nx, ny=ny, L0=nx / 128.0, Phi_tolerance=1e-9, T_tolerance=1e-9, Phi_max_iters=30, T_max_iters=30, **kw)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+
+    def run():
+        with S.Solver(nx, ny, dtype) as s:
+            F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+            infos, launches0 = [], s.kernel_launches
+            for _ in range(4):
+                info = s.step(p, F, U, nF, nU)
+                infos.append((info.Phi_iters, info.T_iters, info.Phi_converged, info.T_converged, info.Phi_error, info.T_error))
+                F, nF = nF, F; U, nU = nU, U
+            return s.download(F), s.download(U), infos, s.kernel_launches - launches0
+
+    monkeypatch.delenv("PF_SI_PER_KERNEL", raising=False)
+    cF, cU, cinfo, claunches = run()
+    monkeypatch.setenv("PF_SI_PER_KERNEL", "1")
+    kF, kU, kinfo, klaunches = run()
+    assert np.array_equal(cF, kF) and np.array_equal(cU, kU)
+    assert cinfo == kinfo, (cinfo, kinfo)
+    assert claunches < klaunches / 10, (claunches, klaunches)          # the cooperative path really ran
+
+
 # ---- libdevice ----------------------------------------------------------------------------------------------------------------
 def test_libdevice_restatement_bit_identical_on_gpu():
     from _helpers.probe import Probe
