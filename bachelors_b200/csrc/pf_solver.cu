@@ -58,6 +58,10 @@ struct pf_solver {
     int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
     cudaStream_t aux_stream = nullptr;      // second stream: boundary rows of a slab run here while the interior runs on `stream`
     cudaStream_t launch_stream = nullptr;   // stream the next fused launch goes to (stream or aux_stream)
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // pf_step_host: copy streams (created on first use)
+    enum { HOST_BANDS_MAX = 32 };
+    cudaEvent_t ev_up[HOST_BANDS_MAX] = {}, ev_done[HOST_BANDS_MAX] = {};
+    cudaEvent_t ev_host_begin = nullptr;
     int64_t launches = 0;
     std::string err;
 
@@ -199,6 +203,10 @@ void pf_destroy(pf_solver* s)
     if(s->h_cg) cudaFreeHost(s->h_cg);
     if(s->h_stats) cudaFreeHost(s->h_stats);
     if(s->aux_stream) { cudaStreamSynchronize(s->aux_stream); cudaStreamDestroy(s->aux_stream); }
+    if(s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }
+    if(s->d2h_stream) { cudaStreamSynchronize(s->d2h_stream); cudaStreamDestroy(s->d2h_stream); }
+    for(int i = 0; i < pf_solver::HOST_BANDS_MAX; i++) { if(s->ev_up[i]) cudaEventDestroy(s->ev_up[i]); if(s->ev_done[i]) cudaEventDestroy(s->ev_done[i]); }
+    if(s->ev_host_begin) cudaEventDestroy(s->ev_host_begin);
     if(s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -1043,6 +1051,88 @@ int pf_step_rows_async(pf_solver* s, const pf_params* params, const void* F, con
     RowWindow w(s, y_begin, y_end, on_aux_stream);
     return s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
                               : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
+}
+
+// sim_modify(UPLOAD) x2 + sim_step + sim_modify(DOWNLOAD) x2 as ONE call (main.cpp:164-168, :553, :857): the host hands
+// in y(n) and gets y(n+1) back. For the fixed-step explicit solvers on the single-kernel path the three legs are
+// pipelined over row bands: band b+1 uploads while band b computes while band b-1 downloads (a band needs `ghost` rows
+// of its neighbours, so its kernel waits for the upload of band b+1). PCIe is full duplex, so the step costs about one
+// direction's copy time instead of upload + compute + download. Everything else takes the plain sequence.
+int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, const void* host_U, void* host_next_F, void* host_next_U,
+                 int host_dtype, void* F, void* U, void* next_F, void* next_U, pf_step_info* info)
+{
+    if(int rc = bind(s)) return rc;
+    if(!host_F || !host_U || !host_next_F || !host_next_U) return fail(s, PF_ERR_INVALID, "pf_step_host: NULL host pointer");
+    if(int rc = check_step_args(s, params, F, U, next_F, next_U)) return rc;
+    const size_t count = (size_t) s->nx * (size_t) s->slab.ny_local;
+    const size_t first = (size_t) s->ghost_lo * (size_t) s->nx;            // element offset of the first owned row
+    const size_t rs = s->real_size();
+    char *dF = (char*) F + first * rs, *dU = (char*) U + first * rs, *dnF = (char*) next_F + first * rs, *dnU = (char*) next_U + first * rs;
+    const bool pipelined = host_dtype == s->dtype && s->is_full_grid() &&
+        (params->solver == PF_SOLVER_EXPLICIT_EULER || params->solver == PF_SOLVER_EXPLICIT_RK4) &&
+        !params->do_corrector_loop && !params->do_stats && !params->do_stats_step_residual && fused_eligible(s, *params) &&
+        (s->last_num_steps % 2) == 0 && s->ny >= 64;
+    if(!pipelined)
+    {
+        if(int rc = pf_upload(s, dF, host_F, count, host_dtype)) return rc;
+        if(int rc = pf_upload(s, dU, host_U, count, host_dtype)) return rc;
+        if(int rc = pf_step(s, params, F, U, next_F, next_U, info)) return rc;
+        if(int rc = pf_download(s, dnF, host_next_F, count, host_dtype)) return rc;
+        return pf_download(s, dnU, host_next_U, count, host_dtype);
+    }
+    if(!s->h2d_stream)
+    {
+        PF_CUDA(s, cudaStreamCreateWithFlags(&s->h2d_stream, cudaStreamNonBlocking));
+        PF_CUDA(s, cudaStreamCreateWithFlags(&s->d2h_stream, cudaStreamNonBlocking));
+        PF_CUDA(s, cudaEventCreateWithFlags(&s->ev_host_begin, cudaEventDisableTiming));
+        for(int i = 0; i < pf_solver::HOST_BANDS_MAX; i++)
+        {
+            PF_CUDA(s, cudaEventCreateWithFlags(&s->ev_up[i], cudaEventDisableTiming));
+            PF_CUDA(s, cudaEventCreateWithFlags(&s->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    // bands of >= 64 rows, at most HOST_BANDS_MAX; 16 bands keep the pipeline fill at ~1/16 of a copy
+    const int ny = s->ny;
+    const int nb = std::max(1, std::min<int>({16, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
+    const int rows_per = (ny + nb - 1) / nb;
+    const size_t row_bytes = (size_t) s->nx * rs;
+    // the copies must not overtake work already queued on the solver's stream that still reads or writes these fields
+    PF_CUDA(s, cudaEventRecord(s->ev_host_begin, s->stream));
+    PF_CUDA(s, cudaStreamWaitEvent(s->h2d_stream, s->ev_host_begin, 0));
+    int bands = 0;
+    for(int y0 = 0; y0 < ny; y0 += rows_per, bands++)
+    {
+        const int y1 = std::min(ny, y0 + rows_per);
+        const size_t off = (size_t) y0 * row_bytes, bytes = (size_t)(y1 - y0) * row_bytes;
+        PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+        PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+        PF_CUDA(s, cudaEventRecord(s->ev_up[bands], s->h2d_stream));
+    }
+    for(int b = 0; b < bands; b++)
+    {
+        const int y0 = b * rows_per, y1 = std::min(ny, y0 + rows_per);
+        PF_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_up[std::min(b + 1, bands - 1)], 0));     // rows y1 .. y1+ghost live in the next band
+        {
+            RowWindow w(s, y0, y1, 0);
+            int rc = s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
+                                        : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
+            if(rc) return rc;
+        }
+        PF_CUDA(s, cudaEventRecord(s->ev_done[b], s->stream));
+        PF_CUDA(s, cudaStreamWaitEvent(s->d2h_stream, s->ev_done[b], 0));
+        const size_t off = (size_t) y0 * row_bytes, bytes = (size_t)(y1 - y0) * row_bytes;
+        PF_CUDA(s, cudaMemcpyAsync((char*) host_next_F + off, dnF + off, bytes, cudaMemcpyDeviceToHost, s->d2h_stream));
+        PF_CUDA(s, cudaMemcpyAsync((char*) host_next_U + off, dnU + off, bytes, cudaMemcpyDeviceToHost, s->d2h_stream));
+    }
+    PF_CUDA(s, cudaStreamSynchronize(s->d2h_stream));
+    PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    if(info)
+    {
+        memset(info, 0, sizeof *info);
+        info->dt_advanced = params->dt;
+        info->Phi_iters = 1; info->T_iters = 1;
+    }
+    return PF_OK;
 }
 
 int pf_rkm_attempt_rows_async(pf_solver* s, const pf_params* params, double tau, const void* F, const void* U, void* next_F, void* next_U,

@@ -19,7 +19,7 @@ EXPORTS = [
     "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download", "pf_upload_raw", "pf_download_raw",
     "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
-    "pf_step", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
+    "pf_step", "pf_step_host", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
 ]
 
@@ -62,6 +62,7 @@ def lib():
         "pf_rkm_decide": (i32, [vp, P(pf_params), dbl, C.c_uint64, C.c_uint64, P(i32), P(i32), P(dbl), P(dbl), P(dbl)]),
         "pf_rkm_finish_async": (i32, [vp, P(pf_params), dbl, dbl, vp, vp, vp, vp]),
         "pf_step": (i32, [vp, P(pf_params), vp, vp, vp, vp, P(pf_step_info)]),
+        "pf_step_host": (i32, [vp, P(pf_params), vp, vp, vp, vp, i32, vp, vp, vp, vp, P(pf_step_info)]),
         "pf_run": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, P(vp), P(vp), P(i64), P(dbl), P(pf_step_info)]),
         "pf_step_async": (i32, [vp, P(pf_params), vp, vp, vp, vp]), "pf_sync": (i32, [vp]), "pf_stream": (vp, [vp]),
         "pf_rhs": (i32, [vp, P(pf_params), i32, P(dbl), P(vp), P(vp), vp, vp]),
@@ -170,6 +171,15 @@ class Solver:
     def step(self, params, F, U, next_F, next_U):
         info = pf_step_info()
         self._ck(lib().pf_step(self._h, C.byref(params), F, U, next_F, next_U, C.byref(info)))
+        return info
+
+    def step_host(self, params, host_F, host_U, host_next_F, host_next_U, F, U, next_F, next_U):
+        """upload + step + download in one call (numpy arrays or raw host pointers of the solver's dtype)."""
+        def ptr(a):
+            return a.ctypes.data if hasattr(a, "ctypes") else a
+        info = pf_step_info()
+        self._ck(lib().pf_step_host(self._h, C.byref(params), ptr(host_F), ptr(host_U), ptr(host_next_F), ptr(host_next_U),
+                                    self.dtype, F, U, next_F, next_U, C.byref(info)))
         return info
 
     def step_async(self, params, F, U, next_F, next_U):

@@ -221,32 +221,41 @@ def time_device_steps(runner, torch, steps, world, dist):
 
 
 def time_e2e(runner, torch, steps, world, dist):
-    """The reference-facing call sequence with HOST buffers: every step uploads (Phi, T) from pinned host memory
-    (sim_modify UPLOAD), steps once (sim_step, which returns after a device synchronisation, simulation.cu:1153) and
-    downloads the result (sim_modify DOWNLOAD). Wall clock bracketed by synchronize; max over ranks."""
+    """The reference-facing call with HOST buffers: every step hands y(n) in pinned host memory to pf_step_host (= sim_modify
+    UPLOAD x2 + sim_step + sim_modify DOWNLOAD x2, main.cpp:164-168/:553/:857) and gets y(n+1) back in host memory; the output
+    buffers of one step are the input buffers of the next. Wall clock bracketed by synchronize; max over ranks.
+    N > 1: each rank moves its own slab; the ghost rows of the uploaded state are exchanged before the step."""
     own_F, own_U = runner.owned(runner.F), runner.owned(runner.U)
-    hF = torch.empty(own_F.shape, dtype=own_F.dtype).pin_memory()
-    hU = torch.empty(own_U.shape, dtype=own_U.dtype).pin_memory()
-    hF.copy_(own_F); hU.copy_(own_U)
-    nbytes = hF.numel() * hF.element_size() * 2
-    s, L = runner.solver, None
+    hA = [torch.empty(own_F.shape, dtype=own_F.dtype).pin_memory() for _ in range(2)]
+    hB = [torch.empty(own_F.shape, dtype=own_F.dtype).pin_memory() for _ in range(2)]
+    hA[0].copy_(own_F); hA[1].copy_(own_U)
+    nbytes = hA[0].numel() * hA[0].element_size() * 2
     from bachelors_b200 import solver as S
-    L = S.lib()
+    from bachelors_b200._abi import pf_step_info
+    s, L = runner.solver, S.lib()
     dt_code = runner.dtype
+    p = runner.params
     runner.sync()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
-        s._ck(L.pf_upload(s._h, runner.owned(runner.F).data_ptr(), hF.data_ptr(), hF.numel(), dt_code))
-        s._ck(L.pf_upload(s._h, runner.owned(runner.U).data_ptr(), hU.data_ptr(), hU.numel(), dt_code))
-        if world > 1:
+        if world == 1:
+            info = pf_step_info()
+            s._ck(L.pf_step_host(s._h, C.byref(p), hA[0].data_ptr(), hA[1].data_ptr(), hB[0].data_ptr(), hB[1].data_ptr(), dt_code,
+                                 runner.F.data_ptr(), runner.U.data_ptr(), runner.nF.data_ptr(), runner.nU.data_ptr(), C.byref(info)))
+            runner.F, runner.nF = runner.nF, runner.F
+            runner.U, runner.nU = runner.nU, runner.U
+        else:
+            s._ck(L.pf_upload(s._h, runner.owned(runner.F).data_ptr(), hA[0].data_ptr(), hA[0].numel(), dt_code))
+            s._ck(L.pf_upload(s._h, runner.owned(runner.U).data_ptr(), hA[1].data_ptr(), hA[1].numel(), dt_code))
             runner.exchange(runner.F, runner.U)          # the uploaded rows' halos (host data changed the owned rows)
-        runner.step()
-        runner.sync()
-        s._ck(L.pf_download(s._h, runner.owned(runner.F).data_ptr(), hF.data_ptr(), hF.numel(), dt_code))
-        s._ck(L.pf_download(s._h, runner.owned(runner.U).data_ptr(), hU.data_ptr(), hU.numel(), dt_code))
+            runner.step()
+            runner.sync()
+            s._ck(L.pf_download(s._h, runner.owned(runner.F).data_ptr(), hB[0].data_ptr(), hB[0].numel(), dt_code))
+            s._ck(L.pf_download(s._h, runner.owned(runner.U).data_ptr(), hB[1].data_ptr(), hB[1].numel(), dt_code))
+        hA, hB = hB, hA
     torch.cuda.synchronize()
     secs = time.perf_counter() - t0
     if world > 1:
@@ -339,7 +348,7 @@ def run_cuda_arm(args):
                      "kernel": kernel_name, "peak_source": peak_src,
                      "algorithmic_bytes_per_cell_step": alg_per_cell, "launches_per_step": launches_per_step},
         "e2e": {"value": e2e_glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h * world,
-                "steps": e2e_steps, "what": "pf_upload(Phi,T) from pinned host + pf_step + pf_download(Phi,T) every step"},
+                "steps": e2e_steps, "what": "pf_step_host every step: y(n) from pinned host memory in, y(n+1) to pinned host memory out (upload + step + download; banded and overlapped for explicit / explicit-rk4 at N = 1)"},
         "gpu_launches": tot_launches,
         "clocks": clocks,
         "sim_time_advanced": t_adv,
@@ -404,9 +413,31 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
-    if args.impl == "reference":
-        return run_reference_arm(args)
-    return run_cuda_arm(args)
+    # The contract is ONE JSON line on stdout. Libraries write banners to fd 1 (NCCL prints its version line there), so
+    # everything but the final line goes to stderr: fd 1 is pointed at fd 2 for the run and restored for the print.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    captured = []
+    import builtins
+    _print = builtins.print
+
+    def print_line(*a, **k):
+        if k.get("file") in (None, sys.stdout) and len(a) == 1 and isinstance(a[0], str) and a[0].startswith("{"):
+            captured.append(a[0])
+        else:
+            _print(*a, **k)
+    builtins.print = print_line
+    try:
+        rc = run_reference_arm(args) if args.impl == "reference" else run_cuda_arm(args)
+    finally:
+        builtins.print = _print
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    for line in captured:
+        print(line, flush=True)
+    return rc
 
 
 if __name__ == "__main__":

@@ -179,6 +179,17 @@ PF_API int  pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void
                    int64_t n_steps, double stop_time,
                    void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info);
 
+/* The reference host's per-step sequence with HOST fields as ONE call: sim_modify(F, UPLOAD), sim_modify(U, UPLOAD)
+ * (main.cpp:164-168), sim_step (main.cpp:553), sim_modify(next_F, DOWNLOAD), sim_modify(next_U, DOWNLOAD) (main.cpp:857).
+ * host_F / host_U (y(n)) and host_next_F / host_next_U (y(n+1)) are dense nx x ny_local arrays of host_dtype (pinned memory
+ * lets the copies overlap); F, U, next_F, next_U are device fields of this solver that receive the same data.
+ * For explicit / explicit-rk4 on the single-kernel path upload, compute and download are pipelined over row bands
+ * (full-duplex PCIe); every other configuration runs upload, pf_step, download in sequence. Returns after the
+ * results are in host memory. */
+PF_API int  pf_step_host(pf_solver* s, const pf_params* params,
+                         const void* host_F, const void* host_U, void* host_next_F, void* host_next_U, int host_dtype,
+                         void* F, void* U, void* next_F, void* next_U, pf_step_info* info);
+
 /* Asynchronous variants for host-side pipelining: enqueue on the solver's stream, return immediately.
  * Fixed-step solvers only (the adaptive solver needs its error norm on the host to answer dt). */
 PF_API int  pf_step_async(pf_solver* s, const pf_params* params,

@@ -442,6 +442,36 @@ def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, dtype, m
     assert claunches < klaunches / 10, (claunches, klaunches)          # the cooperative path really ran
 
 
+@pytest.mark.parametrize("solver,dtype,host_dtype", [("explicit-rk4", PF_F64, PF_F64), ("explicit", PF_F64, PF_F64), ("explicit-rk4", PF_F32, PF_F32),
+                                                     ("explicit-rk4", PF_F64, PF_F32), ("explicit-rk4-adaptive", PF_F64, PF_F64), ("semi-implicit", PF_F64, PF_F64)])
+def test_step_host_equals_upload_step_download(solver, dtype, host_dtype):
+    """pf_step_host (banded upload / compute / download pipeline for the fixed-step explicit solvers) returns exactly what the
+    three separate calls return, over several steps with the outputs fed back as inputs."""
+    nx, ny = 333, 700
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_tolerance=1e-7, T_tolerance=1e-7)
+    npdt = np.float64 if host_dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    with S.Solver(nx, ny, dtype) as a, S.Solver(nx, ny, dtype) as b:
+        aF, aU, anF, anU = a.field_alloc(), a.field_alloc(), a.field_alloc(), a.field_alloc()
+        bF, bU, bnF, bnU = b.field_alloc(), b.field_alloc(), b.field_alloc(), b.field_alloc()
+        hF, hU = F0.copy(), U0.copy()
+        gF, gU = F0.copy(), U0.copy()
+        for _ in range(3):
+            oF, oU = np.empty_like(hF), np.empty_like(hU)
+            L = S.lib()
+            info = S.pf_step_info()
+            import ctypes
+            a._ck(L.pf_step_host(a._h, ctypes.byref(p), hF.ctypes.data, hU.ctypes.data, oF.ctypes.data, oU.ctypes.data, host_dtype, aF, aU, anF, anU, ctypes.byref(info)))
+            b.upload(bF, gF); b.upload(bU, gU)
+            winfo = b.step(p, bF, bU, bnF, bnU)
+            wF, wU = b.download(bnF, dtype=npdt), b.download(bnU, dtype=npdt)
+            assert np.array_equal(oF, wF) and np.array_equal(oU, wU)
+            assert info.dt_advanced == winfo.dt_advanced and info.Phi_iters == winfo.Phi_iters
+            hF, hU, gF, gU = oF, oU, wF, wU
+            aF, anF, aU, anU = anF, aF, anU, aU
+            bF, bnF, bU, bnU = bnF, bF, bnU, bU
+
+
 # ---- libdevice ----------------------------------------------------------------------------------------------------------------
 def test_libdevice_restatement_bit_identical_on_gpu():
     from _helpers.probe import Probe
