@@ -1091,9 +1091,13 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
             PF_CUDA(s, cudaEventCreateWithFlags(&s->ev_done[i], cudaEventDisableTiming));
         }
     }
-    // bands of >= 64 rows, at most HOST_BANDS_MAX; 16 bands keep the pipeline fill at ~1/16 of a copy
+    // bands of >= 64 rows, at most HOST_BANDS_MAX. Measured on B200 / PCIe 5 at 2048^2 fp64 (2 x 32 MiB each way): 1 band 2.50 ms,
+    // 4: 2.06, 8: 1.94, 16: 2.16, 32: 2.55 per call - more bands shorten the pipeline fill but every copy and launch costs
+    // host enqueue time; the two copy directions alone need 1.4 ms when overlapped.
     const int ny = s->ny;
-    const int nb = std::max(1, std::min<int>({16, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
+    int want_bands = 8;
+    if(const char* e = getenv("PF_HOST_BANDS")) want_bands = std::max(1, atoi(e));            // tuning hook
+    const int nb = std::max(1, std::min<int>({want_bands, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
     const int rows_per = (ny + nb - 1) / nb;
     const size_t row_bytes = (size_t) s->nx * rs;
     // the copies must not overtake work already queued on the solver's stream that still reads or writes these fields
