@@ -1,7 +1,7 @@
 """ctypes mirrors of the plain-C structs in include/pf_solver.h (keep in sync with PF_ABI_VERSION)."""
 import ctypes as C
 
-PF_ABI_VERSION = 1
+PF_ABI_VERSION = 2
 
 PF_OK, PF_ERR_INVALID, PF_ERR_NO_DEVICE, PF_ERR_CUDA, PF_ERR_OOM, PF_ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
 
@@ -62,6 +62,25 @@ class pf_step_info(C.Structure):
 
 class pf_slab(C.Structure):
     _fields_ = [("y0", C.c_int32), ("ny_local", C.c_int32), ("has_lo", C.c_int32), ("has_hi", C.c_int32), ("ghost", C.c_int32)]
+
+
+class pf_initial(C.Structure):
+    """[initial] section of config.ini (reference config.h:20-30)."""
+    _fields_ = [("inside_phi", C.c_double), ("inside_T", C.c_double), ("outside_phi", C.c_double), ("outside_T", C.c_double),
+                ("circle_center", C.c_double * 2), ("circle_radius", C.c_double), ("circle_fade", C.c_double),
+                ("square_from", C.c_double * 2), ("square_to", C.c_double * 2)]
+
+
+class pf_stats_row(C.Structure):
+    """One line of stats.csv (reference main.cpp:192-234)."""
+    _fields_ = [("time", C.c_double), ("iter", C.c_int64), ("Phi_iters", C.c_int64), ("T_iters", C.c_int64),
+                ("T_delta_L1", C.c_float), ("T_delta_L2", C.c_float), ("T_delta_max", C.c_float), ("T_delta_min", C.c_float),
+                ("Phi_delta_L1", C.c_float), ("Phi_delta_L2", C.c_float), ("Phi_delta_max", C.c_float), ("Phi_delta_min", C.c_float),
+                ("step_res_L1", C.c_float * PF_MAX_STEP_RESIDUALS), ("step_res_L2", C.c_float * PF_MAX_STEP_RESIDUALS),
+                ("step_res_max", C.c_float * PF_MAX_STEP_RESIDUALS), ("step_res_min", C.c_float * PF_MAX_STEP_RESIDUALS)]
+
+
+PF_SNAPSHOT_SLOTS, PF_SNAPSHOT_MAX_FIELDS = 2, 8
 
 
 def default_params(**kw):

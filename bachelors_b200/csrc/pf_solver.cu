@@ -18,6 +18,7 @@
 #include "pf_stream.cuh"
 #include "pf_general.cuh"
 #include "pf_si_coop.cuh"
+#include "pf_app.cuh"
 
 using namespace pf;
 
@@ -62,6 +63,11 @@ struct pf_solver {
     enum { HOST_BANDS_MAX = 32 };
     cudaEvent_t ev_up[HOST_BANDS_MAX] = {}, ev_done[HOST_BANDS_MAX] = {};
     cudaEvent_t ev_host_begin = nullptr;
+    // snapshots (pf_snapshot_*): device staging + pinned host buffer per slot, one copy stream
+    struct SnapSlot { void* dev = nullptr; double* host = nullptr; size_t bytes = 0; int n_fields = 0; cudaEvent_t staged = nullptr, landed = nullptr; bool pending = false; };
+    SnapSlot snap[PF_SNAPSHOT_SLOTS];
+    cudaStream_t snap_stream = nullptr;
+    void* d_rgba = nullptr; size_t rgba_bytes = 0;      // pf_render_rgba
     int64_t launches = 0;
     std::string err;
 
@@ -207,6 +213,15 @@ void pf_destroy(pf_solver* s)
     if(s->d2h_stream) { cudaStreamSynchronize(s->d2h_stream); cudaStreamDestroy(s->d2h_stream); }
     for(int i = 0; i < pf_solver::HOST_BANDS_MAX; i++) { if(s->ev_up[i]) cudaEventDestroy(s->ev_up[i]); if(s->ev_done[i]) cudaEventDestroy(s->ev_done[i]); }
     if(s->ev_host_begin) cudaEventDestroy(s->ev_host_begin);
+    if(s->snap_stream) { cudaStreamSynchronize(s->snap_stream); cudaStreamDestroy(s->snap_stream); }
+    for(auto& sl : s->snap)
+    {
+        if(sl.dev) cudaFree(sl.dev);
+        if(sl.host) cudaFreeHost(sl.host);
+        if(sl.staged) cudaEventDestroy(sl.staged);
+        if(sl.landed) cudaEventDestroy(sl.landed);
+    }
+    if(s->d_rgba) cudaFree(s->d_rgba);
     if(s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -1281,3 +1296,5 @@ int pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* o
 }
 
 } // extern "C"
+
+#include "pf_app_host.inl"

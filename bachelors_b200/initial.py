@@ -10,8 +10,9 @@ def make_initial_conditions(cfg, dtype=np.float64, rows=None):
     xs = (np.arange(nx, dtype=np.float64) + 0.5) / nx * L0
     ys = (np.arange(y0, y1, dtype=np.float64) + 0.5) / ny * L0
     X, Y = np.meshgrid(xs, ys)
-    lo = cfg.init_circle_radius - p.xi * cfg.init_circle_fade / 2
-    hi = cfg.init_circle_radius + p.xi * cfg.init_circle_fade / 2
+    # `Real lo, hi` in the reference (main.cpp:113-114): rounded to the field type before use
+    lo = float(np.dtype(dtype).type(cfg.init_circle_radius - p.xi * cfg.init_circle_fade / 2))
+    hi = float(np.dtype(dtype).type(cfg.init_circle_radius + p.xi * cfg.init_circle_fade / 2))
     r = np.hypot(cfg.init_circle_center[0] - X, cfg.init_circle_center[1] - Y)
     within = ((cfg.init_square_from[0] <= X) & (X < cfg.init_square_to[0]) &
               (cfg.init_square_from[1] <= Y) & (Y < cfg.init_square_to[1]))

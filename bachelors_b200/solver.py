@@ -7,7 +7,8 @@ import os
 
 import numpy as np
 
-from ._abi import (PF_ABI_VERSION, PF_F32, PF_F64, PF_OK, pf_params, pf_step_info, pf_delta_stats, pf_slab)
+from ._abi import (PF_ABI_VERSION, PF_F32, PF_F64, PF_OK, pf_params, pf_step_info, pf_delta_stats, pf_slab, pf_initial,
+                   pf_stats_row)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpfsolver.so")
@@ -21,6 +22,8 @@ EXPORTS = [
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
     "pf_step", "pf_step_host", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
+    "pf_init_fields", "pf_snapshot_begin", "pf_snapshot_wait", "pf_write_maps_bin", "pf_write_maps_bin_header",
+    "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
 ]
 
 
@@ -71,6 +74,14 @@ def lib():
         "pf_stats_delta": (i32, [vp, vp, vp, P(pf_delta_stats)]),
         "pf_halo_region": (i32, [vp, vp, i32, P(vp), P(vp), P(sz)]),
         "pf_kernel_launches": (i64, [vp]),
+        "pf_init_fields": (i32, [vp, P(pf_params), P(pf_initial), vp, vp]),
+        "pf_snapshot_begin": (i32, [vp, i32, i32, P(vp)]), "pf_snapshot_wait": (i32, [vp, i32, P(vp)]),
+        "pf_write_maps_bin": (i32, [C.c_char_p, i32, i32, dbl, dbl, i64, dbl, i32, P(C.c_char_p), P(vp)]),
+        "pf_write_maps_bin_header": (i32, [C.c_char_p, i32, i32, dbl, dbl, i64, dbl, i32, P(C.c_char_p)]),
+        "pf_write_maps_bin_rows": (i32, [C.c_char_p, i32, i32, i32, i32, i32, i32, vp]),
+        "pf_write_stats_csv": (i32, [C.c_char_p, i32, i32, i32, dbl, i32, sz, P(pf_stats_row)]),
+        "pf_render_rgba": (i32, [vp, vp, C.c_float, C.c_float, vp]),
+        "pf_write_png": (i32, [C.c_char_p, i32, i32, vp, i32]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -101,6 +112,7 @@ class Solver:
         self._h = C.c_void_p()
         L = lib()
         self.nx, self.ny, self.dtype, self.device = nx, ny, dtype, device
+        self._slab = slab
         if slab is None:
             rc = L.pf_create(C.byref(self._h), device, dtype, nx, ny)
         else:
@@ -228,7 +240,76 @@ class Solver:
         self._ck(lib().pf_stats_delta(self._h, a, b, C.byref(out)))
         return out
 
+    # -- rows around the stepping path
+    def init_fields(self, params, init, F, U):
+        """Initial conditions evaluated on the device (main.cpp:93-136)."""
+        self._ck(lib().pf_init_fields(self._h, C.byref(params), C.byref(init), F, U))
+
+    def snapshot_begin(self, slot, fields):
+        arr = (C.c_void_p * len(fields))(*fields)
+        self._ck(lib().pf_snapshot_begin(self._h, slot, len(fields), arr))
+        self._snap_n = getattr(self, "_snap_n", {})
+        self._snap_n[slot] = len(fields)
+
+    def snapshot_wait(self, slot, owned_rows=None):
+        """-> list of (rows, nx) float64 views of the slot's pinned host buffers (valid until the slot is reused)."""
+        n = self._snap_n[slot]
+        ptrs = (C.c_void_p * n)()
+        self._ck(lib().pf_snapshot_wait(self._h, slot, ptrs))
+        rows = owned_rows if owned_rows is not None else self.owned_rows
+        out = []
+        for p in ptrs:
+            buf = (C.c_double * (rows * self.nx)).from_address(p)
+            out.append(np.frombuffer(buf, dtype=np.float64).reshape(rows, self.nx))
+        return out
+
+    @property
+    def owned_rows(self):
+        return self.ny if self._slab is None else self._slab.ny_local
+
+    def render_rgba(self, field, display_min, display_max):
+        out = np.empty((self.owned_rows, self.nx, 4), dtype=np.uint8)
+        self._ck(lib().pf_render_rgba(self._h, field, display_min, display_max, out.ctypes.data))
+        return out
+
     def halo_region(self, field, side):
         send, recv, n = C.c_void_p(), C.c_void_p(), C.c_size_t(0)
         self._ck(lib().pf_halo_region(self._h, field, side, C.byref(send), C.byref(recv), C.byref(n)))
         return send.value, recv.value, n.value
+
+
+# ---- output files of the reference host (pure host code in the library: usable without a GPU) -------------------
+def _ck_io(rc):
+    if rc != PF_OK:
+        raise PfError(rc, lib().pf_last_error(None).decode())
+
+
+def write_maps_bin(path, dx, dy, it, time, maps):
+    """maps: {name: (ny, nx) float64 array}; byte-compatible with save_bin_map_file (main.cpp:705-735)."""
+    names = list(maps)
+    arrs = [np.ascontiguousarray(maps[n], dtype=np.float64) for n in names]
+    ny, nx = arrs[0].shape
+    cn = (C.c_char_p * len(names))(*[n.encode() for n in names])
+    cp = (C.c_void_p * len(names))(*[a.ctypes.data for a in arrs])
+    _ck_io(lib().pf_write_maps_bin(path.encode(), nx, ny, dx, dy, it, time, len(names), cn, cp))
+
+
+def write_maps_bin_header(path, nx, ny, dx, dy, it, time, names):
+    cn = (C.c_char_p * len(names))(*[n.encode() for n in names])
+    _ck_io(lib().pf_write_maps_bin_header(path.encode(), nx, ny, dx, dy, it, time, len(names), cn))
+
+
+def write_maps_bin_rows(path, nx, ny, n_maps, map_index, y0, data):
+    data = np.ascontiguousarray(data, dtype=np.float64)
+    _ck_io(lib().pf_write_maps_bin_rows(path.encode(), nx, ny, n_maps, map_index, y0, data.shape[0], data.ctypes.data))
+
+
+def write_stats_csv(path, append, nx, ny, dt, step_res_count, rows):
+    arr = (pf_stats_row * len(rows))(*rows)
+    _ck_io(lib().pf_write_stats_csv(path.encode(), int(append), nx, ny, dt, step_res_count, len(rows), arr))
+
+
+def write_png(path, rgba, flip_y=True):
+    rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+    h, w, _ = rgba.shape
+    _ck_io(lib().pf_write_png(path.encode(), w, h, rgba.ctypes.data, int(flip_y)))

@@ -31,7 +31,7 @@ extern "C" {
 #  define PF_API __attribute__((visibility("default")))
 #endif
 
-#define PF_ABI_VERSION 1
+#define PF_ABI_VERSION 2
 
 typedef enum pf_status {
     PF_OK               =  0,
@@ -246,6 +246,64 @@ PF_API int  pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_
  * side 0 = lo (rows below), 1 = hi. `send` = the first/last `ghost` OWNED rows, `recv` = the ghost rows.
  * The transport (NCCL send/recv or peer copies) is the caller's; rows are contiguous nx*ghost reals. */
 PF_API int  pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, void** recv_ptr, size_t* count);
+
+/* ---- initial conditions on the device --------------------------------- */
+/* The [initial] section of config.ini (Sim_Config, config.h:20-30). */
+typedef struct pf_initial {
+    double inside_phi, inside_T, outside_phi, outside_T;
+    double circle_center[2];
+    double circle_radius, circle_fade;
+    double square_from[2], square_to[2];
+} pf_initial;
+/* sim_make_initial_conditions (main.cpp:93-136) evaluated on the device, straight into the solver's fields (ghost
+ * rows of a slab included): replaces the CPU loop + sim_modify(UPLOAD) x2 of simulation_state_reload (main.cpp:151-173).
+ * All arithmetic in double as on the host, cast to Real at the end. */
+PF_API int  pf_init_fields(pf_solver* s, const pf_params* params, const pf_initial* init, void* F, void* U);
+
+/* ---- snapshots: device -> pinned host, overlapped with stepping -------- */
+enum { PF_SNAPSHOT_SLOTS = 2, PF_SNAPSHOT_MAX_FIELDS = 8 };
+/* Replaces the blocking sim_modify_double(DOWNLOAD) per map of save_state (main.cpp:846-858, simulation.cu:1010-1049).
+ * _begin: the OWNED rows of each field are copied (f32 solvers: converted to double, simulation.cu:1036-1047) into a
+ * device staging buffer in stream order - the caller may step on at once - and from there to a pinned host buffer on
+ * a copy stream. _wait blocks until slot's copy has landed and returns the host pointers (ny_local*nx doubles each,
+ * valid until the slot is used again). Two slots: one can be written to disk while the other fills. */
+PF_API int  pf_snapshot_begin(pf_solver* s, int slot, int n_fields, const void* const* dev_fields);
+PF_API int  pf_snapshot_wait(pf_solver* s, int slot, const double** host_fields);
+
+/* ---- output files of the reference host (pure host code: no device needed) ------------------- */
+/* maps_NNNN.bin, byte for byte what save_bin_map_file writes (main.cpp:705-735; read by plot.py:26-73):
+ * i32 magic 0x11223344, i32 map_count, i32 nx, i32 ny, f64 dx, f64 dy, f64 time, i64 iter, map_count x char[32]
+ * names, map_count x nx*ny f64. */
+PF_API int  pf_write_maps_bin(const char* path, int nx, int ny, double dx, double dy, int64_t iter, double time,
+                              int n_maps, const char* const* names, const double* const* maps);
+/* The same file written in pieces (slabs of several ranks): header first, then any rows of any map in any order. */
+PF_API int  pf_write_maps_bin_header(const char* path, int nx, int ny, double dx, double dy, int64_t iter, double time,
+                                     int n_maps, const char* const* names);
+PF_API int  pf_write_maps_bin_rows(const char* path, int nx, int ny, int n_maps, int map_index, int y0, int rows, const double* data);
+
+/* One line of stats.csv = one App_Stats sample (main.cpp:192-234); floats as the reference stores them (Sim_Stats, simulation.h:57-81). */
+typedef struct pf_stats_row {
+    double  time;
+    int64_t iter;
+    int64_t Phi_iters, T_iters;
+    float   T_delta_L1, T_delta_L2, T_delta_max, T_delta_min;
+    float   Phi_delta_L1, Phi_delta_L2, Phi_delta_max, Phi_delta_min;
+    float   step_res_L1[PF_MAX_STEP_RESIDUALS], step_res_L2[PF_MAX_STEP_RESIDUALS];
+    float   step_res_max[PF_MAX_STEP_RESIDUALS], step_res_min[PF_MAX_STEP_RESIDUALS];
+} pf_stats_row;
+/* save_csv_stat_file (main.cpp:741-757, 782-825): header lines unless `append`, then one line per row, every number
+ * through the reference's 16-byte "%f" / "%lli" strings. */
+PF_API int  pf_write_stats_csv(const char* path, int append, int nx, int ny, double dt, int step_res_count,
+                               size_t n_rows, const pf_stats_row* rows);
+
+/* ---- headless view ----------------------------------------------------- */
+/* The viewer's fragment shader (gl.h:221-283: NaN -> magenta, grey arctangent ramps outside [min, max], 4-segment
+ * blue-cyan-green-yellow-red inside) evaluated by a CUDA kernel over the owned rows of a field (sampled as float,
+ * gl.h:396), RGBA8 into host memory (ny_local*nx*4 bytes, row y of the grid = row y of the buffer). The GL window,
+ * swap chain and texture upload of the reference are not reproduced. */
+PF_API int  pf_render_rgba(pf_solver* s, const void* dev_field, float display_min, float display_max, uint8_t* host_rgba);
+/* Minimal PNG writer (8-bit RGBA, stored deflate blocks). flip_y != 0 puts grid row 0 at the bottom, as the viewer does. */
+PF_API int  pf_write_png(const char* path, int width, int height, const uint8_t* rgba, int flip_y);
 
 /* ---- counters -------------------------------------------------------------------------------- */
 PF_API int64_t pf_kernel_launches(const pf_solver* s);      /* kernels launched by this solver so far (bench.py: gpu_launches) */

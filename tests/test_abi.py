@@ -6,7 +6,8 @@ import re
 import pytest
 
 from bachelors_b200 import solver
-from bachelors_b200._abi import PF_ERR_NO_DEVICE, PF_F64, pf_params, pf_step_info, pf_slab, pf_delta_stats
+from bachelors_b200._abi import (PF_ERR_NO_DEVICE, PF_F64, pf_params, pf_step_info, pf_slab, pf_delta_stats, pf_initial,
+                                  pf_stats_row)
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -35,7 +36,7 @@ def test_no_other_default_visibility_symbols():
 
 def test_abi_version_and_sizes():
     L = solver.lib()
-    assert L.pf_abi_version() == 1
+    assert L.pf_abi_version() == 2
     assert L.pf_sizeof_real(PF_F64) == 8 and L.pf_sizeof_real(0) == 4
     assert [L.pf_required_ghost(s) for s in (1, 2, 3, 4)] == [1, 4, 5, 1]
 
@@ -44,14 +45,15 @@ def test_struct_layouts_match_header():
     """sizeof of the ctypes mirrors == sizeof in C (compiled from the header with gcc)."""
     import subprocess
     import tempfile
-    src = '#include "pf_solver.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu\\n", sizeof(pf_params), sizeof(pf_step_info), sizeof(pf_slab), sizeof(pf_delta_stats));return 0;}\n'
+    src = '#include "pf_solver.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(pf_params), sizeof(pf_step_info), sizeof(pf_slab), sizeof(pf_delta_stats), sizeof(pf_initial), sizeof(pf_stats_row));return 0;}\n'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
         open(c, "w").write(src)
         exe = os.path.join(d, "s")
         subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe], check=True)
         sizes = [int(x) for x in subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()]
-    assert sizes == [C.sizeof(pf_params), C.sizeof(pf_step_info), C.sizeof(pf_slab), C.sizeof(pf_delta_stats)]
+    assert sizes == [C.sizeof(pf_params), C.sizeof(pf_step_info), C.sizeof(pf_slab), C.sizeof(pf_delta_stats), C.sizeof(pf_initial),
+                     C.sizeof(pf_stats_row)]
 
 
 def test_create_fails_loudly_without_device():
