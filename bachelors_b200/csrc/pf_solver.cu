@@ -462,7 +462,7 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     }
     const int own_rows = a.own_y1 - a.own_y0;
     if(own_rows <= 0) return PF_OK;
-    const int strips = (a.nx + EWI - 1) / EWI;
+    const int strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
     const int nch = stream_chunks(s->sm_count, MINB, strips, own_rows, (SK + 1) * (NST - 1));
     a.chunk = (own_rows + nch - 1) / nch;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;

@@ -4,8 +4,8 @@
 // Replaces, for one time step, the reference's 1 (Euler) / 5 (RK4) / >=7 (Merson) launches of
 // explicit_solver_solve_lin_combination + combine + reductions (reference simulation.cu:283-497).
 //
-// One CTA of EW = 32*WARPS threads owns a column strip: thread cx owns global column gx = strip_x0 - H + cx
-// (H = #stages; the H columns on each side are halo) and walks down a chunk of rows. In iteration `it` the thread
+// One CTA of EW = 32*WARPS threads owns a column strip: thread cx owns one global column (H = #stages columns on each
+// side of the strip are halo, except towards a non-periodic domain edge, where none is needed) and walks down a chunk of rows. In iteration `it` the thread
 // evaluates stage s on row g1 - SK*(s-1), g1 = G0 + it being the row of stage 1 and SK the skew:
 //   SK = 1: stage s+1 consumes, as its N neighbour, what stage s has produced in the same iteration (least state,
 //           but the stages of one row form one dependency chain);
@@ -312,6 +312,14 @@ struct StreamIters {
     }
 };
 
+// Number of column strips of width EW = EWI + 2H threads that cover nx columns (see the kernel for the ownership rule).
+static inline __host__ __device__ int stream_strips(int nx, int EWI, int H, bool periodic)
+{
+    if(periodic) return (nx + EWI - 1) / EWI;
+    const int n = (nx - 2 * H + EWI - 1) / EWI;                         // (n-1)*EWI + EW >= nx
+    return n < 1 ? 1 : n;
+}
+
 template <typename Real, int SCHEME, int WARPS, int SK>
 constexpr size_t stream_smem_bytes()
 {
@@ -335,15 +343,21 @@ k_stream_step(const FusedArgs<Real> a)
 
     StreamCtx<Real> c;
     const int cx = threadIdx.x;
-    const int strip_x0 = (int) blockIdx.x * EWI;
-    const int gx = strip_x0 - H + cx;
+    // Periodic: strip k owns columns [k*EWI, (k+1)*EWI), its threads start H columns to the left (wrapped).
+    // Non-periodic: nothing outside the domain is needed (the edge thread publishes the ghost pair itself), so thread 0 of
+    // strip 0 IS column 0, and every column of the first / last strip up to the domain edge is clean:
+    // strip k owns [k*EWI + (k ? H : 0), (k+1)*EWI + H), the last one everything up to nx - 1 (see stream_strips).
+    const int gx0 = (int) blockIdx.x * EWI - (periodic ? H : 0);       // column of thread 0
+    const int gx = gx0 + cx;
     if(periodic) { int lx = gx % nx; if(lx < 0) lx += nx; c.lx = (size_t) lx; }
     else         c.lx = (size_t)(gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx));
     c.x_lo_edge = !periodic && gx == 0;
     c.x_hi_edge = !periodic && gx == nx - 1;
     c.wr_self = periodic || (gx != -1 && gx != nx);
-    c.st_ok = cx >= H && cx < EW - H && gx < nx;
-    c.edge_cta = !periodic && (strip_x0 - H <= 0 || strip_x0 - H + EW >= nx);
+    const int cx_lo = (!periodic && gx0 == 0) ? 0 : H;                  // left domain edge inside the CTA: no garbage enters from the left
+    const int cx_hi = (!periodic && gx0 + EW >= nx) ? EW : EW - H;      // right domain edge inside the CTA: none from the right
+    c.st_ok = cx >= cx_lo && cx < cx_hi && gx < nx;
+    c.edge_cta = !periodic && (gx0 <= 0 || gx0 + EW >= nx);
     c.out_off = (size_t)((long long) gx - (long long) a.row0 * (long long) nx);
     c.Y0 = a.own_y0 + (int) blockIdx.y * a.chunk;
     c.Y1 = min(c.Y0 + a.chunk, a.own_y1);

@@ -170,3 +170,18 @@ def test_headless_run_writes_the_reference_files(tmp_path, solver_name, dtype):
         assert all(int(l.split(",")[2]) >= 1 for l in lines[2:])                 # CG iterations of the Phi solve
     else:
         assert np.array_equal(last["maps"]["F"], oF.astype(np.float64)) and np.array_equal(last["maps"]["U"], oU.astype(np.float64))
+
+
+def test_full_size_adaptive_run_takes_the_published_number_of_steps(tmp_path):
+    """the reference's adaptive solver needs 9522 steps (A100; 9523 on the other GPU) to t = 0.04 at
+    2048^2 with tolerances 5e-9 (benchmark_ellapsed_times.txt:112,199). The whole run, 11 snapshots included."""
+    over = "[snapshot]\nfolder = %s" % tmp_path
+    out = run_config(os.path.join(ROOT, "benchmark_configs", "config_explicit-rk4-adaptive_2048.ini"), PF_F64, overrides=[over])
+    assert abs(out["iters"] - 9522) <= 2
+    assert out["snapshots"] == 10 and len(out["files"]) == 11
+    last = load_bin_map_file(out["files"][-1])
+    assert last["nx"] == 2048 and last["iter"] == out["iters"] and last["time"] >= 0.04 - 1e-16
+    F = last["maps"]["F"]
+    assert np.isfinite(F).all() and F.min() > -0.1 and F.max() < 1.1
+    assert np.array_equal(F, F[::-1]) and np.array_equal(F, F[:, ::-1])         # the seed is centred: the dendrite stays symmetric
+    assert F.sum() > load_bin_map_file(out["files"][0])["maps"]["F"].sum() * 4   # and it grew

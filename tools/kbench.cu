@@ -89,7 +89,7 @@ static void launch_stream(FusedArgs<Real> a, int nch)
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     a.chunk = chunk;
-    dim3 grid((a.nx + EWI - 1) / EWI, (a.own_y1 - a.own_y0 + chunk - 1) / chunk), block(32 * WARPS);
+    dim3 grid(stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC), (a.own_y1 - a.own_y0 + chunk - 1) / chunk), block(32 * WARPS);
     kern<<<grid, block, smem>>>(a);
 }
 
