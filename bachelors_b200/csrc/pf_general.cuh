@@ -188,11 +188,13 @@ __device__ __forceinline__ void si_prepare_cell(const Real* __restrict__ F, cons
 template <typename Real, bool ANISO>
 __global__ void __launch_bounds__(256)
 k_si_prepare(const Real* __restrict__ F, const Real* __restrict__ U, Real* __restrict__ b_F, Real* __restrict__ factor_out,
-             int nx, int ny, int F_bound, int U_bound, KConsts<Real> k)
+             int nx, int ny, int F_bound, int U_bound, KConsts<Real> k, int y_begin = 0, int y_end = 0x7fffffff)
 {
+    // rows [y_begin, y_end) of the ny rows the pointers hold: a slab passes its allocation (ghost rows included, so
+    // the y-neighbours of an owned row are plain memory) and the window of its owned rows
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    if(x >= nx || y >= ny) return;
+    const int y = y_begin + blockIdx.y * blockDim.y + threadIdx.y;
+    if(x >= nx || y >= ny || y >= y_end) return;
     const size_t i = (size_t) x + (size_t) y * (size_t) nx;
     Real right, factor;
     si_prepare_cell<Real, ANISO>(F, U, x, y, nx, ny, F_bound, U_bound, k, right, factor);
@@ -220,6 +222,7 @@ struct CgMatrix {
     Real X, Y, C_minus_one;      // A_Phi: -dt/dx^2, -dt/dy^2, 2dt/dx^2 + 2dt/dy^2   (simulation.cu:772-776)
     Real C, R, Lc, Uc, D;        // A_T                                              (simulation.cu:782-787)
     int nx, ny, boundary;
+    int y_begin, y_end;          // rows the kernels produce (all of [0, ny) on a full grid; the owned rows of a slab)
 };
 
 // (A*vec)(x, y); `sc` is the per-cell factor of A_Phi at this cell (ignored for A_T).
@@ -287,13 +290,13 @@ k_cg_init(CgMatrix<Real> A, const Real* __restrict__ x0, const Real* __restrict_
           Real* __restrict__ p, Real* __restrict__ rr_partials, CgState* st, int max_iters)
 {
     __shared__ Real scratch[32];
-    const int nx = A.nx, ny = A.ny;
+    const int nx = A.nx;
     const int segs = (nx + CG_THREADS - 1) / CG_THREADS;
-    const int items = segs * ny;
+    const int items = segs * (A.y_end - A.y_begin);
     Real acc = 0;
     for(int wi = blockIdx.x; wi < items; wi += gridDim.x)
     {
-        const int y = wi / segs, xx = (wi % segs) * CG_THREADS + threadIdx.x;
+        const int y = A.y_begin + wi / segs, xx = (wi % segs) * CG_THREADS + threadIdx.x;
         if(xx < nx)
         {
             const size_t i = (size_t) xx + (size_t) y * (size_t) nx;
@@ -316,13 +319,13 @@ k_cg_spmv(CgMatrix<Real> A, const Real* __restrict__ p, Real* __restrict__ Ap, R
 {
     if(st->done) return;
     __shared__ Real scratch[32];
-    const int nx = A.nx, ny = A.ny;
+    const int nx = A.nx;
     const int segs = (nx + CG_THREADS - 1) / CG_THREADS;
-    const int items = segs * ny;
+    const int items = segs * (A.y_end - A.y_begin);
     Real acc = 0;
     for(int wi = blockIdx.x; wi < items; wi += gridDim.x)
     {
-        const int y = wi / segs, xx = (wi % segs) * CG_THREADS + threadIdx.x;
+        const int y = A.y_begin + wi / segs, xx = (wi % segs) * CG_THREADS + threadIdx.x;
         if(xx < nx)
         {
             const size_t i = (size_t) xx + (size_t) y * (size_t) nx;

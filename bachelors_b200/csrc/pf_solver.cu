@@ -68,6 +68,8 @@ struct pf_solver {
     SnapSlot snap[PF_SNAPSHOT_SLOTS];
     cudaStream_t snap_stream = nullptr;
     void* d_rgba = nullptr; size_t rgba_bytes = 0;      // pf_render_rgba
+    // pf_si_*: the semi-implicit step in phases (slabs); what pf_si_begin_async was given
+    struct SiCtx { pf_params p; const void *F = nullptr, *U = nullptr, *U_base = nullptr; void *nF = nullptr, *nU = nullptr; bool active = false; } si;
     int64_t launches = 0;
     std::string err;
 
@@ -773,7 +775,7 @@ static CgMatrix<Real> make_matrix(const pf_params& p, int which, const Real* fac
 {
     CgMatrix<Real> A; memset(&A, 0, sizeof A);
     const Real dt = (Real) p.dt, dx = (Real) p.L0 / p.nx, dy = (Real) p.L0 / p.ny;
-    A.which = which; A.factor = factor; A.nx = p.nx; A.ny = p.ny;
+    A.which = which; A.factor = factor; A.nx = p.nx; A.ny = p.ny; A.y_begin = 0; A.y_end = p.ny;
     if(which == 0)
     {
         A.C_minus_one = 2 * dt / (dx * dx) + 2 * dt / (dy * dy);          // simulation.cu:774-776
@@ -1298,3 +1300,4 @@ int pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* o
 } // extern "C"
 
 #include "pf_app_host.inl"
+#include "pf_si_slab.inl"

@@ -171,9 +171,9 @@ class SlabRunner:
             self.last_attempts = 1
         elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE:
             dt = self._step_adaptive(p, F, U, nF, nU)
+        elif self.world > 1:
+            dt = self._step_semi_implicit(p, F, U, nF, nU)
         else:
-            if self.world > 1:
-                raise S.PfError(-5, "SlabRunner: the semi-implicit solver is single-GPU only in this version")
             # one sim_step-shaped call: returns after the device finished (the CG iteration counts come back with it)
             info = pf_step_info()
             s._ck(L.pf_step(s._h, C.byref(p), F, U, nF, nU, C.byref(info)))
@@ -220,6 +220,48 @@ class SlabRunner:
         s._ck(L.pf_rkm_finish_async(s._h, C.byref(p), used, tau, F, U, nF, nU))
         self.last_attempts = attempts
         return used
+
+    # -- semi-implicit solver on slabs: phases of the library + all-gathered partial sums + one-row exchange of p ------------
+    def _si_setup(self):
+        L, s = S.lib(), self.solver
+        dev = torch.device("cuda", self.device)
+        tdt = torch.float64 if self.dtype == PF_F64 else torch.float32
+        mine = torch.tensor([L.pf_si_partials(s._h)], dtype=torch.int64, device=dev)
+        widths = [torch.zeros_like(mine) for _ in range(self.world)]
+        dist.all_gather(widths, mine, group=self.group)
+        width = max(int(w.item()) for w in widths)
+        n_all = width * self.world
+        t = {k: torch.zeros(n, dtype=tdt, device=dev) for k, n in (("part", width), ("rr0", n_all), ("rr1", n_all), ("pAp", n_all))}
+        self._si_t = t
+        self._si_by_ptr = {v.data_ptr(): v for v in t.values()}
+        self._si_bufs = [{k: v.data_ptr() for k, v in t.items()} | {"width": width, "n_all": n_all}]
+        typestr = "<f8" if self.dtype == PF_F64 else "<f4"
+        self._si_dir = torch.as_tensor(_DevArray(L.pf_si_direction(s._h), (s.rows_alloc, self.params.nx), typestr), device=dev)
+        torch.cuda.synchronize(self.device)
+
+    def _step_semi_implicit(self, p, F, U, nF, nU):
+        from .slabs import semi_implicit_step_phases
+        if not hasattr(self, "_si_bufs"):
+            self._si_setup()
+        s = self.solver
+
+        def gather(_solvers, src, dst):
+            dist.all_gather_into_tensor(self._si_by_ptr[dst[0]], self._si_by_ptr[src[0]], group=self.group)
+
+        def exchange_direction(_solvers):
+            exchange_halos([self._si_dir], 1, s.first_owned_row, self.layout.ny_local, self.lo, self.hi, self.group)
+
+        # everything in the order of the solver's own stream: its kernels, the collectives, the row exchanges
+        self.main.wait_event(self.ev_halo)
+        with torch.cuda.stream(self.main):
+            iters, conv, errs = semi_implicit_step_phases([s], p, [[F, U, nF, nU]], self._si_bufs, gather, exchange_direction)
+            exchange_halos([self.nF, self.nU], self.ghost, s.first_owned_row, self.layout.ny_local, self.lo, self.hi, self.group)
+            self.ev_halo.record(self.main)
+            self.ev_main.record(self.main)
+        self.last_attempts = 1
+        self.last_cg_iters = iters
+        self.last_cg_errors = errs
+        return p.dt
 
     def close(self):
         self.sync()

@@ -24,6 +24,8 @@ EXPORTS = [
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
     "pf_init_fields", "pf_snapshot_begin", "pf_snapshot_wait", "pf_write_maps_bin", "pf_write_maps_bin_header",
     "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
+    "pf_si_begin_async", "pf_si_partials", "pf_si_cg_begin_async", "pf_si_cg_spmv_async", "pf_si_cg_update_async",
+    "pf_si_cg_pupdate_async", "pf_si_direction", "pf_si_cg_poll",
 ]
 
 
@@ -82,6 +84,10 @@ def lib():
         "pf_write_stats_csv": (i32, [C.c_char_p, i32, i32, i32, dbl, i32, sz, P(pf_stats_row)]),
         "pf_render_rgba": (i32, [vp, vp, C.c_float, C.c_float, vp]),
         "pf_write_png": (i32, [C.c_char_p, i32, i32, vp, i32]),
+        "pf_si_begin_async": (i32, [vp, P(pf_params), vp, vp, vp, vp, vp]), "pf_si_partials": (i32, [vp]),
+        "pf_si_cg_begin_async": (i32, [vp, i32, vp]), "pf_si_cg_spmv_async": (i32, [vp, i32, vp]),
+        "pf_si_cg_update_async": (i32, [vp, i32, vp, vp, i32, vp]), "pf_si_cg_pupdate_async": (i32, [vp, i32, vp, vp, i32, i32]),
+        "pf_si_direction": (vp, [vp]), "pf_si_cg_poll": (i32, [vp, i32, P(i32), P(i32), P(i32), P(dbl)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)

@@ -247,6 +247,34 @@ PF_API int  pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_
  * The transport (NCCL send/recv or peer copies) is the caller's; rows are contiguous nx*ghost reals. */
 PF_API int  pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, void** recv_ptr, size_t* count);
 
+/* ---- semi-implicit solver on slabs: the step in phases --------------------- */
+/* semi_implicit_solver_step_based (simulation.cu:732-926) cut where ranks must talk. The library has no communication
+ * code; per time step the caller runs, on every rank in lock step (all calls enqueue on pf_stream and return):
+ *   pf_si_begin_async                          prepare kernel (needs 1 current ghost row of F and U)
+ *   for which in {0 = Phi, 1 = T}:
+ *     pf_si_cg_begin_async(which, part)        b_T (which = 1), r = b - A x0, p = r; `part` <- pf_si_partials() partial sums of r.r
+ *     ALL-GATHER part -> rr_all                (n_all = sum of the ranks' pf_si_partials(), rank order)
+ *     repeat max_iters times (or until pf_si_cg_poll reports done; the flag is identical on all ranks):
+ *       EXCHANGE one ghost row of pf_si_direction() with the neighbours (pf_halo_region gives the rows)
+ *       pf_si_cg_spmv_async(which, part)       Ap = A p, partial sums of p.Ap            -> ALL-GATHER -> pAp_all
+ *       pf_si_cg_update_async(.., rr_all, pAp_all, n_all, part)   x, r update, partials of the new r.r -> ALL-GATHER -> rr_new_all
+ *       pf_si_cg_pupdate_async(.., rr_all, rr_new_all, n_all, it) convergence test, p update; then rr_all <-> rr_new_all
+ *   EXCHANGE the ghost rows of next_F, next_U before the next step.
+ * Every rank folds the same gathered partials in the same order, so alpha, beta and the stop decision are bit-identical
+ * across ranks. Against the single-GPU run only the summation tree differs (rel-L2 <= 1e-10 fp64, iterations +-1).
+ * `part` and the gathered arrays are device memory of the solver's Real type. */
+PF_API int   pf_si_begin_async(pf_solver* s, const pf_params* params, const void* F, const void* U, const void* U_base,
+                               void* next_F, void* next_U);
+PF_API int   pf_si_partials(pf_solver* s);
+PF_API int   pf_si_cg_begin_async(pf_solver* s, int which, void* partials_out);
+PF_API int   pf_si_cg_spmv_async(pf_solver* s, int which, void* partials_out);
+PF_API int   pf_si_cg_update_async(pf_solver* s, int which, const void* rr_all, const void* pAp_all, int n_all, void* partials_out);
+PF_API int   pf_si_cg_pupdate_async(pf_solver* s, int which, const void* rr_all, const void* rr_new_all, int n_all, int iter);
+PF_API void* pf_si_direction(pf_solver* s);                  /* the search direction p, laid out like a field (ghost rows included) */
+/* Synchronises pf_stream and reads the solve's control block: done flag, iterations (loop index at break, simulation.cu:681),
+ * converged, sqrt(r.r/N). */
+PF_API int   pf_si_cg_poll(pf_solver* s, int which, int* done, int* iters, int* converged, double* error);
+
 /* ---- initial conditions on the device --------------------------------- */
 /* The [initial] section of config.ini (Sim_Config, config.h:20-30). */
 typedef struct pf_initial {

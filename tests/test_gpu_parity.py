@@ -488,3 +488,56 @@ def test_libdevice_restatement_bit_identical_on_gpu():
                             ("cosf", oracle.cosf(c), pr.cosf(c))):
         same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
         assert same.all(), (name, int((~same).sum()), a[~same][:3], b[~same][:3], c[~same][:3])
+
+
+# ---- semi-implicit solver on slabs: phases + gathered partial sums -----------------------------------
+@pytest.mark.parametrize("bc", ["neumann", "periodic", "dirichlet"])
+@pytest.mark.parametrize("dtype,S_aniso", [(PF_F64, 0.0), (PF_F64, 0.25), (PF_F32, 0.0)])
+def test_semi_implicit_slabs_match_the_single_grid(bc, dtype, S_aniso):
+    """Three slabs on one device, stepped in lock step through the pf_si_* phases with the all-gather and the one-row
+    exchange of the search direction done through the host. Against the single-grid solver only the summation tree of the
+    dot products differs: rel-L2 <= 1e-10 (fp64) / 1e-5 (fp32), CG iteration counts within +-1 (north_star)."""
+    from bachelors_b200.slabs import (host_exchange_rows, make_host_gather, semi_implicit_buffers, semi_implicit_step_phases,
+                                      slab_layout)
+    nx, ny, G, steps = 150, 131, 3, 4
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    p = default_params(solver="semi-implicit", nx=nx, ny=ny, L0=nx / 128.0, S=S_aniso, Phi_boundary=bc, T_boundary=bc, gamma=0.75,
+                       Phi_tolerance=1e-9 if dtype == PF_F64 else 1e-5, T_tolerance=1e-9 if dtype == PF_F64 else 1e-5)
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    want_F, want_U, _, want_info = cuda_replay(p, F0, U0, dtype, steps)
+    periodic = bc == "periodic"
+    slabs = [slab_layout(ny, G, g, 1, periodic=periodic) for g in range(G)]
+    solvers = [S.Solver(nx, ny, dtype, slab=sl) for sl in slabs]
+    L = S.lib()
+    try:
+        def padded(a, sl, s):
+            rows = np.arange(s.rows_alloc) - s.first_owned_row + sl.y0
+            return a[rows % ny if periodic else np.clip(rows, 0, ny - 1)]
+        st = [[s.field_from(padded(F0, sl, s)), s.field_from(padded(U0, sl, s)), s.field_alloc(), s.field_alloc()] for sl, s in zip(slabs, solvers)]
+        bufs = semi_implicit_buffers(solvers)
+        gather = make_host_gather(bufs[0]["width"])
+
+        def exchange_direction(solvers_):
+            for s in solvers_:
+                s.sync()
+            host_exchange_rows(solvers_, slabs, [L.pf_si_direction(s._h) for s in solvers_], ny, periodic)
+
+        q = p.copy()
+        got_info = []
+        for i in range(steps):
+            q.iter = i; q.time = i * p.dt
+            iters, conv, errs = semi_implicit_step_phases(solvers, q, st, bufs, gather, exchange_direction, poll_every=1)
+            got_info.append(iters)
+            for f in st:
+                f[0], f[2] = f[2], f[0]; f[1], f[3] = f[3], f[1]
+            full_F = host_exchange_rows(solvers, slabs, [f[0] for f in st], ny, periodic)
+            full_U = host_exchange_rows(solvers, slabs, [f[1] for f in st], ny, periodic)
+        tol = tol_of(dtype)
+        assert rel_l2(full_F, want_F) <= tol and rel_l2(full_U, want_U) <= tol
+        for (gi_F, gi_T), w in zip(got_info, want_info):
+            assert abs(gi_F - int(w[1])) <= 1 and abs(gi_T - int(w[2])) <= 1
+        if dtype == PF_F64:
+            assert max(max(i) for i in got_info) >= 2                # the solves really iterate
+    finally:
+        for s in solvers:
+            s.close()
