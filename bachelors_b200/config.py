@@ -138,7 +138,7 @@ def read_config_text(text, overrides=()):
             setattr(cfg, attr, v)
 
     def solver(s):
-        if s not in SOLVER_NAMES or s == "none":
+        if s not in SOLVER_NAMES or s == "none":                 # "exact" is accepted (simulation.h:158-170)
             raise ValueError(s)
         return SOLVER_NAMES[s]
 
@@ -208,8 +208,20 @@ def read_config_text(text, overrides=()):
     else:
         cfg.scale = 1.0
 
-    if p.do_exact:
-        raise ConfigError("do_exact = true is out of scope (reference marks it 'slightly broken', simulation.h:17)")
+    if p.do_exact:                                              # config.h:492-509: the analytic test case overrides the physics
+        A = 1.0 / 16
+        h = max(p.L0 / p.nx, p.L0 / p.ny)
+        p.Tm = 0
+        p.L = 1
+        if p.solver != SOLVER_NAMES["exact"]:
+            p.dt = A / 4 * h * h
+        p.a = 1
+        p.b = 1
+        p.alpha = 1
+        p.beta = 1 / 0.001
+        p.S = 0
+        p.xi = p.L0 / p.nx * 11 / 10
+        cfg.init_circle_radius = 0.25
     if missing:
         raise ConfigError("couldnt find or parse some config entries: " + ", ".join(missing))
     return cfg

@@ -14,6 +14,7 @@ struct InitArgs {
     double L0, xi;
     int nx, ny_global;
     int row0, rows;          // global row of local row 0, rows to fill (ghost rows included)
+    int do_exact;            // analytic initial profile (main.cpp:104-110) instead of the circle / square blend
     int wrap;                // ghost rows outside [0, ny) hold the periodic image (else the clamped row; never read)
 };
 
@@ -47,6 +48,14 @@ k_init_fields(const InitArgs a, Real* __restrict__ F, Real* __restrict__ U)
     // main.cpp:101: ((x+0.5)) / nx * L0, left to right, in double
     const double px = ((double) x + 0.5) / (double) a.nx * a.L0;
     const double py = ((double) gy + 0.5) / (double) a.ny_global * a.L0;
+    const size_t i = (size_t) ly * (size_t) a.nx + (size_t) x;
+    if(a.do_exact)
+    {
+        const Real r = (Real) hypot_cr(px - a.L0 / 2, py - a.L0 / 2);                  // main.cpp:106
+        F[i] = exact_phi_ini<Real>(r, (Real) a.xi);
+        U[i] = exact_u<Real>((Real) 0, r);
+        return;
+    }
     // main.cpp:113-114: lo/hi are Real in the reference; for Real = float they are rounded to float first
     const Real lo_r = (Real)(a.radius - a.xi * a.fade / 2);
     const Real hi_r = (Real)(a.radius + a.xi * a.fade / 2);
@@ -58,7 +67,6 @@ k_init_fields(const InitArgs a, Real* __restrict__ F, Real* __restrict__ U)
     if(circle < 0) circle = 0;
     const double cube = within ? 1 : 0;
     const double factor = cube > circle ? cube : circle;
-    const size_t i = (size_t) ly * (size_t) a.nx + (size_t) x;
     F[i] = (Real)(factor * a.inside_phi + (1 - factor) * a.outside_phi);
     U[i] = (Real)(factor * a.inside_T + (1 - factor) * a.outside_T);
 }

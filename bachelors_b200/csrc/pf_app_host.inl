@@ -9,7 +9,6 @@ int pf_init_fields(pf_solver* s, const pf_params* params, const pf_initial* init
     if(int rc = bind(s)) return rc;
     if(!params || !init || !F || !U) return fail(s, PF_ERR_INVALID, "pf_init_fields: NULL argument");
     if(params->nx != s->nx || params->ny != s->ny) return fail(s, PF_ERR_INVALID, "pf_init_fields: params %dx%d != solver %dx%d", params->nx, params->ny, s->nx, s->ny);
-    if(params->do_exact) return fail(s, PF_ERR_UNSUPPORTED, "pf_init_fields: do_exact initial conditions are out of scope");
     InitArgs a;
     a.inside_phi = init->inside_phi; a.inside_T = init->inside_T; a.outside_phi = init->outside_phi; a.outside_T = init->outside_T;
     a.cx = init->circle_center[0]; a.cy = init->circle_center[1]; a.radius = init->circle_radius; a.fade = init->circle_fade;
@@ -17,6 +16,7 @@ int pf_init_fields(pf_solver* s, const pf_params* params, const pf_initial* init
     a.L0 = params->L0; a.xi = params->xi;
     a.nx = s->nx; a.ny_global = s->ny;
     a.row0 = s->slab.y0 - s->ghost_lo; a.rows = s->rows_alloc;
+    a.do_exact = params->do_exact != 0;
     a.wrap = params->Phi_boundary == PF_BOUNDARY_PERIODIC;
     dim3 block(256), grid((unsigned)((s->nx + 255) / 256), (unsigned) s->rows_alloc);
     if(s->dtype == PF_F64) k_init_fields<double><<<grid, block, 0, s->stream>>>(a, (double*) F, (double*) U);

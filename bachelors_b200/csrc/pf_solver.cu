@@ -512,6 +512,7 @@ static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, c
 static bool fused_eligible(const pf_solver* s, const pf_params& p)
 {
     if(p.Phi_boundary != p.T_boundary) return false;                 // mixed boundary types: general path
+    if(p.do_exact) return false;                                      // nonzero source term fu in every stage: general per-stage path
     if(p.Phi_boundary == PF_BOUNDARY_PERIODIC && (s->slab.has_lo != s->slab.has_hi)) return false;
     return true;
 }
@@ -956,8 +957,15 @@ static int step_impl(pf_solver* s, const pf_params& p, const void* F_, const voi
         case PF_SOLVER_EXPLICIT_RK4_ADAPTIVE:
             if(int rc = rk4_adaptive_step<Real>(s, p, F, U, nF, nU, info, &dt)) return rc;
             break;
-        case PF_SOLVER_EXACT:
-            return fail(s, PF_ERR_UNSUPPORTED, "solver = exact is out of scope (reference marks it 'slightly broken', simulation.h:17)");
+        case PF_SOLVER_EXACT:                                               // exact_solver_step, :1069-1089, :1118-1121
+        {
+            if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "solver = exact is single-GPU only");
+            dim3 grid((unsigned)((s->nx + 255) / 256), (unsigned) s->ny);
+            k_exact_fields<Real><<<grid, 256, 0, s->stream>>>(s->nx, s->ny, (Real) p.L0 / p.nx, (Real) p.L0 / p.ny, (Real) p.L0, (Real) p.time, nF, nU);
+            PF_LAUNCH_CHECK(s);
+            dt = p.dt;
+            break;
+        }
         default:
             return fail(s, PF_ERR_INVALID, "unknown solver %d", p.solver);
     }
@@ -987,7 +995,7 @@ static int check_step_args(pf_solver* s, const pf_params* p, const void* F, cons
     if(!p || !F || !U || !nF || !nU) return fail(s, PF_ERR_INVALID, "pf_step: NULL argument");
     if(p->nx != s->nx || p->ny != s->ny)                                    // simulation.cu:1094-1095
         return fail(s, PF_ERR_INVALID, "Bad sizes provided: params %dx%d, solver %dx%d", p->nx, p->ny, s->nx, s->ny);
-    if(p->do_exact) return fail(s, PF_ERR_UNSUPPORTED, "do_exact is out of scope");
+    if(p->do_exact && !s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "do_exact is single-GPU only");
     if(F == nF || U == nU) return fail(s, PF_ERR_INVALID, "pf_step: in-place stepping is not supported");
     for(int b : {p->Phi_boundary, p->T_boundary})
         if(b < PF_BOUNDARY_PERIODIC || b > PF_BOUNDARY_NEUMANN_ZERO) return fail(s, PF_ERR_INVALID, "bad boundary type %d", b);

@@ -39,7 +39,7 @@ typedef enum pf_status {
     PF_ERR_NO_DEVICE    = -2,  /* no CUDA device / driver */
     PF_ERR_CUDA         = -3,  /* a CUDA call failed; see pf_last_error() */
     PF_ERR_OOM          = -4,
-    PF_ERR_UNSUPPORTED  = -5,  /* e.g. solver = exact / do_exact (out of scope) */
+    PF_ERR_UNSUPPORTED  = -5,  /* e.g. the corrector loop or do_exact on a slab */
 } pf_status;
 
 /* Storage/arithmetic type of the fields: the reference's compile-time `Real`
@@ -63,7 +63,7 @@ typedef enum pf_solver_type {
     PF_SOLVER_EXPLICIT_RK4          = 2,  /* "explicit-rk4"          */
     PF_SOLVER_EXPLICIT_RK4_ADAPTIVE = 3,  /* "explicit-rk4-adaptive" */
     PF_SOLVER_SEMI_IMPLICIT         = 4,  /* "semi-implicit"         */
-    PF_SOLVER_EXACT                 = 5,  /* "exact" - PF_ERR_UNSUPPORTED */
+    PF_SOLVER_EXACT                 = 5,  /* "exact": writes the analytic fields at params.time (simulation.cu:1069-1089) */
 } pf_solver_type;
 
 /* The numeric content of Sim_Params (simulation.h:83-130) without the host pointers
@@ -93,7 +93,7 @@ typedef struct pf_params {
     int32_t do_corrector_guess;  /* bool */
     int32_t do_stats;            /* bool: fill pf_step_info delta statistics (simulation.cu:1126-1142) */
     int32_t do_stats_step_residual; /* bool (simulation.cu:979-993) */
-    int32_t do_exact;            /* must be 0 */
+    int32_t do_exact;            /* bool: source term fu = exact_fu(iter*dt) in the explicit RHS (simulation.cu:179-184); single GPU */
 } pf_params;
 
 enum { PF_MAX_STEP_RESIDUALS = 20 };   /* MAX_STEP_RESIDUALS, simulation.h:56 */

@@ -29,6 +29,62 @@
   #define POW(a, b) powf((a), (b))
 #endif
 
+#if ORC_IS_DOUBLE
+  #define EXPR(a) exp(a)
+  #define ERFR(a) erf(a)
+  #define HYPOTR(a, b) hypot((a), (b))
+#else
+  #define EXPR(a) expf(a)
+  #define ERFR(a) erff(a)
+  #define HYPOTR(a, b) hypotf((a), (b))
+#endif
+
+/* The analytic ("exact") mode: reference exact.h:17-96, all in Real arithmetic. Static parameters exact.h:90-96. */
+#define ORC_EXACT_LAMBDA  ((REAL) 0.5)
+#define ORC_EXACT_R_INI   ((REAL) 0.25)
+#define ORC_EXACT_EPSILON ((REAL) 0.001)
+static inline REAL FN(orc_exact_R)(REAL t) { return SQRT(ORC_EXACT_R_INI * ORC_EXACT_R_INI + 2 * ORC_EXACT_LAMBDA * t); }      /* exact.h:17-20 */
+static inline REAL FN(orc_exact_U)(REAL Rt) { return -ORC_EXACT_EPSILON * (ORC_EXACT_LAMBDA + 2) / Rt; }                        /* exact.h:22-25 */
+static inline REAL FN(orc_exact_T)(REAL s)                                                                                       /* exact.h:27-35 */
+{
+    REAL l = ORC_EXACT_LAMBDA;
+    REAL pi = (REAL) 3.14159265359;
+    REAL sqrtl2 = SQRT(l / 2);
+    REAL integral = EXPR(-l / 2) - 1 / s * EXPR(-l / 2 * s * s) + sqrtl2 * pi * (ERFR(sqrtl2) - ERFR(s * sqrtl2));
+    return -l * EXPR(l / 2) * integral;
+}
+static inline REAL FN(orc_exact_fu)(REAL t)                                                                                      /* exact.h:37-42 */
+{
+    REAL Rt = FN(orc_exact_R)(t);
+    REAL l = ORC_EXACT_LAMBDA;
+    return ORC_EXACT_EPSILON * l * (l + 2) / (Rt * Rt * Rt);
+}
+static inline REAL FN(orc_exact_u)(REAL t, REAL r)                                                                               /* exact.h:44-53 */
+{
+    REAL Rt = FN(orc_exact_R)(t);
+    REAL ut = FN(orc_exact_U)(Rt);
+    if(r > Rt) ut += FN(orc_exact_T)(r / Rt);
+    return ut;
+}
+static inline REAL FN(orc_exact_phi)(REAL t, REAL r) { return r <= FN(orc_exact_R)(t) ? (REAL) 1 : (REAL) 0; }                  /* exact.h:55-58 */
+
+/* exact_solver_step: reference simulation.cu:1069-1089. `((Real) xi + 0.5)*dx - L0/2` promotes to double for Real = float. */
+static void FN(orc_exact_step)(const pf_params* p, REAL* next_F, REAL* next_U)
+{
+    const REAL dx = (REAL) p->L0 / p->nx, dy = (REAL) p->L0 / p->ny, L0 = (REAL) p->L0, t = (REAL) p->time;
+    const int nx = p->nx, ny = p->ny;
+    #pragma omp parallel for schedule(static)
+    for(int yi = 0; yi < ny; yi++)
+        for(int xi = 0; xi < nx; xi++)
+        {
+            REAL x = (REAL)(((REAL) xi + 0.5) * dx - L0 / 2);
+            REAL y = (REAL)(((REAL) yi + 0.5) * dy - L0 / 2);
+            REAL r = HYPOTR(x, y);
+            next_U[(size_t) xi + (size_t) yi * (size_t) nx] = FN(orc_exact_u)(t, r);
+            next_F[(size_t) xi + (size_t) yi * (size_t) nx] = FN(orc_exact_phi)(t, r);
+        }
+}
+
 /* custom_hypot / custom_atan2 / custom_cos: reference simulation.cu:14-17 (float math, cast back to Real). */
 static inline REAL FN(orc_custom_hypot)(REAL y, REAL x) { return (REAL) orc_hypotf((float) y, (float) x); }
 static inline REAL FN(orc_custom_atan2)(REAL y, REAL x) { return (REAL) orc_atan2f((float) y, (float) x); }
@@ -147,7 +203,7 @@ static void FN(orc_rhs)(const pf_params* p, int is_euler, int n_states, const RE
 {
     FN(orc_consts) c = FN(orc_make_consts)(p);
     const int nx = c.nx, ny = c.ny;
-    const REAL fu = 0;   /* do_exact unsupported: fu = 0 (:179-184) */
+    const REAL fu = p->do_exact ? FN(orc_exact_fu)(p->iter * c.dt) : 0;          /* :179-184 */
     #pragma omp parallel for schedule(static)
     for(int y = 0; y < ny; y++)
     {
@@ -647,6 +703,8 @@ static double FN(orc_step)(orc_state* s, const pf_params* p, const REAL* F, cons
             FN(orc_rk4_step)(s, p, F, U, next_F, next_U, info); dt = p->dt; break;
         case PF_SOLVER_EXPLICIT_RK4_ADAPTIVE:
             dt = FN(orc_rk4_adaptive_step)(s, p, F, U, next_F, next_U, info); break;
+        case PF_SOLVER_EXACT:
+            FN(orc_exact_step)(p, next_F, next_U); dt = p->dt; break;            /* :1118-1121 */
         default: break;
     }
     if(p->do_stats)
@@ -689,6 +747,9 @@ static void FN(orc_debug_values)(const pf_params* p, const REAL* F, const REAL* 
 #undef FMA
 #undef SQRT
 #undef POW
+#undef EXPR
+#undef ERFR
+#undef HYPOTR
 #undef FN
 #undef CAT
 #undef CAT_

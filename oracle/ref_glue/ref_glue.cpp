@@ -67,7 +67,7 @@ static Sim_Params to_sim_params(const pf_params* p, Sim_Stats* stats)
     q.do_debug = false;
     q.do_stats = p->do_stats != 0;
     q.do_stats_step_residual = p->do_stats_step_residual != 0;
-    q.do_exact = false;
+    q.do_exact = p->do_exact != 0;
     q.do_prints = true;          // so that the CG iteration counts reach the capture logger
     q.stats = stats;
     q.temp_maps = NULL; q.temp_map_count = 0;

@@ -301,7 +301,7 @@ def test_errors_are_returned_not_fatal():
             s.step(default_params(nx=64, ny=32), F, U, nF, nU)           # reference: "Bad sizes provided", simulation.cu:1094
         assert e.value.code == PF_ERR_INVALID
         with pytest.raises(S.PfError) as e:
-            s.step(default_params(nx=32, ny=32, solver="exact"), F, U, nF, nU)
+            s.step_async(default_params(nx=32, ny=32, solver="explicit-rk4-adaptive"), F, U, nF, nU)   # dt is a host decision
         assert e.value.code == PF_ERR_UNSUPPORTED
         with pytest.raises(S.PfError) as e:
             s.step(default_params(nx=32, ny=32), F, U, F, nU)
