@@ -183,5 +183,6 @@ def test_full_size_adaptive_run_takes_the_published_number_of_steps(tmp_path):
     assert last["nx"] == 2048 and last["iter"] == out["iters"] and last["time"] >= 0.04 - 1e-16
     F = last["maps"]["F"]
     assert np.isfinite(F).all() and F.min() > -0.1 and F.max() < 1.1
-    assert np.array_equal(F, F[::-1]) and np.array_equal(F, F[:, ::-1])         # the seed is centred: the dendrite stays symmetric
+    # the seed is centred: the dendrite stays mirror-symmetric to rounding ((W - 2C) + E is not bitwise symmetric in E, W)
+    assert np.allclose(F, F[::-1], rtol=1e-6, atol=1e-9) and np.allclose(F, F[:, ::-1], rtol=1e-6, atol=1e-9)
     assert F.sum() > load_bin_map_file(out["files"][0])["maps"]["F"].sum() * 4   # and it grew
