@@ -169,8 +169,14 @@ class SlabRunner:
                          lambda a, b: s._ck(L.pf_step_rows_async(s._h, C.byref(p), F, U, nF, nU, a, b, 0)))
             dt = p.dt
             self.last_attempts = 1
-        elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE:
+        elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and self.world > 1:
             dt = self._step_adaptive(p, F, U, nF, nU)
+        elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE:
+            # one rank: the library's own attempt / decide loop (one 16-byte read-back per attempt, no cross-stream hops)
+            info = pf_step_info()
+            s._ck(L.pf_step(s._h, C.byref(p), F, U, nF, nU, C.byref(info)))
+            dt = info.dt_advanced
+            self.last_attempts = info.Phi_iters
         elif self.world > 1:
             dt = self._step_semi_implicit(p, F, U, nF, nU)
         else:

@@ -292,6 +292,12 @@ def run_cuda_arm(args):
     p = cfg.params
     y0, y1 = slab_rows(p.ny, world, rank)
     F0, U0 = make_initial_conditions(cfg, npdt, rows=(y0, y1))
+    if args.field != "seed":
+        # the dendrite seed has an exactly flat far field; throughput is also reported on a smooth and a seeded-noise state
+        from bachelors_b200.testing import seeded_fields
+        gF, gU = seeded_fields(p.nx, p.ny, npdt, kind=args.field)
+        F0, U0 = np.ascontiguousarray(gF[y0:y1]), np.ascontiguousarray(gU[y0:y1])
+        desc += f", field = {args.field}"
 
     runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap)
     runner.upload_global(F0, U0)
@@ -339,7 +345,7 @@ def run_cuda_arm(args):
     line = {
         "metric": "GLUPS", "value": glups, "unit": "1e9 cell updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": args.dtype, "data": "synthetic (config's dendrite seed; no dataset)",
+        "dtype": args.dtype, "data": ("synthetic (config's dendrite seed; no dataset)" if args.field == "seed" else f"synthetic ({args.field} field of SURVEY 8d; no dataset)"),
         "config": {"workload": desc, "solver": args.solver, "nx": p.nx, "ny": p.ny, "parallelism": f"y-slabs x{world}",
                    "l2_policy": ("working set (2 fields in + 2 out) %.0f MB per GPU vs 126 MB L2; consecutive time steps, no flush"
                                  % (4 * rs * cells / world / 1e6)),
@@ -404,6 +410,8 @@ def main():
     ap.add_argument("--solver", default="explicit-rk4", choices=[k for k in SOLVER_NAMES if k not in ("none", "exact")])
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--size", type=int, default=0, help="N = 1: grid size of the benchmark config (128 ... 2048; default 2048, semi-implicit 1024)")
+    ap.add_argument("--field", default="seed", choices=["seed", "smooth", "noise"],
+                    help="initial state: the config's dendrite seed (default, flat far field), or the smooth / seeded-noise fields of SURVEY 8d")
     ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
     ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
     ap.add_argument("--no-cpu", action="store_true")
