@@ -252,6 +252,53 @@ __device__ __forceinline__ Real cg_apply_sc(const CgMatrix<Real>& A, const Real*
     return val;
 }
 
+// boundary_sample of the vector r + beta*p that has not been stored yet (the cooperative step fuses the p update into
+// the next SpMV): same index rule and same ghost value (0 - v outside a Dirichlet edge) as bsample, v formed on the fly.
+template <typename Real>
+__device__ __forceinline__ Real bsample_axpy(const Real* __restrict__ p, const Real* __restrict__ r, Real beta, int x, int y, int nx, int ny, int bound)
+{
+    if(bound == PF_BOUNDARY_PERIODIC)
+    {
+        if(x < 0) x += nx; else if(x >= nx) x -= nx;
+        if(y < 0) y += ny; else if(y >= ny) y -= ny;
+        const size_t i = (size_t) x + (size_t) y * (size_t) nx;
+        return pf_fma(beta, p[i], r[i]);
+    }
+    const bool inside = x >= 0 && x < nx && y >= 0 && y < ny;
+    const int cx = x < 0 ? 0 : (x >= nx ? nx - 1 : x);
+    const int cy = y < 0 ? 0 : (y >= ny ? ny - 1 : y);
+    const size_t i = (size_t) cx + (size_t) cy * (size_t) nx;
+    const Real v = pf_fma(beta, p[i], r[i]);
+    if(bound == PF_BOUNDARY_DIRICHLET_ZERO && !inside) return (Real) 0 - v;
+    return v;
+}
+
+// (A*(r + beta*p))(x, y) with the centre value c = r + beta*p at (x, y) supplied by the caller: cg_apply_sc on the fly.
+template <typename Real>
+__device__ __forceinline__ Real cg_apply_axpy(const CgMatrix<Real>& A, const Real* __restrict__ p, const Real* __restrict__ r, Real beta,
+                                              Real c, int x, int y, Real sc)
+{
+    const int nx = A.nx, ny = A.ny;
+    const Real e = bsample_axpy(p, r, beta, x + 1, y, nx, ny, A.boundary);
+    const Real w = bsample_axpy(p, r, beta, x - 1, y, nx, ny, A.boundary);
+    const Real n = bsample_axpy(p, r, beta, x, y + 1, nx, ny, A.boundary);
+    const Real s = bsample_axpy(p, r, beta, x, y - 1, nx, ny, A.boundary);
+    Real val;
+    if(A.which == 0)
+    {
+        const Real X = A.X * sc, Y = A.Y * sc;
+        const Real Cc = pf_fma(A.C_minus_one, sc, (Real) 1);
+        val = c * Cc;
+        val = pf_fma(e, X, val); val = pf_fma(w, X, val); val = pf_fma(n, Y, val); val = pf_fma(s, Y, val);
+    }
+    else
+    {
+        val = c * A.C;
+        val = pf_fma(e, A.R, val); val = pf_fma(w, A.Lc, val); val = pf_fma(n, A.Uc, val); val = pf_fma(s, A.D, val);
+    }
+    return val;
+}
+
 template <typename Real>
 __device__ __forceinline__ Real cg_apply(const CgMatrix<Real>& A, const Real* __restrict__ vec, int x, int y)
 {

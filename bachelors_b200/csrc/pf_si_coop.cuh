@@ -7,7 +7,7 @@
 // At the reference's sizes (<= 2048^2) a CG iteration moves a few tens of MB that sit in the 126 MB L2, so the cost of
 // a step is launch and synchronisation latency, not bytes: the per-kernel path (pf_general.cuh, still used when the
 // grid cannot be co-resident) needs 2 x (1 + 3 x max_iters) launches per step whatever the iteration count. Here one
-// launch runs everything, phases separated by cooperative grid barriers (3 per CG iteration + 3 per step), all scalars
+// launch runs everything, phases separated by cooperative grid barriers (2 per CG iteration + 4 per step), all scalars
 // (alpha, beta, the convergence test) recomputed identically by every block from the per-block partial sums in a fixed
 // order. The work decomposition, the arithmetic and the summation trees are those of k_cg_init / k_cg_spmv /
 // k_cg_update / k_cg_pupdate, so the results are bit-identical to the per-kernel path. The right-hand sides b_Phi and
@@ -22,7 +22,7 @@ template <typename Real>
 struct SiCoopArgs {
     const Real* F; const Real* U; const Real* U_base;   // y(n); U_base differs from U only inside the corrector loop
     Real* nF; Real* nU;                                  // y(n+1)
-    Real* factor; Real* r; Real* p; Real* Ap;            // scratch fields
+    Real* factor; Real* r; Real* p; Real* p2; Real* Ap;   // scratch fields (p2: the second buffer of the search direction)
     Real* rr0; Real* rr1; Real* pAp;                     // per-block partial sums (CG_MAX_BLOCKS each)
     CgState* st;                                         // [0] Phi solve, [1] T solve
     CgMatrix<Real> A_F, A_U;
@@ -34,9 +34,13 @@ struct SiCoopArgs {
 };
 
 // The CG iterations after r, p, x and the partials of r.r (in rr0) have been set up: reference simulation.cu:649-690.
+// Two grid barriers per iteration: the p update of iteration it (p = r + beta p, simulation.cu:676) is not a phase of its
+// own but is folded into the SpMV of iteration it + 1, which forms r + beta*p at the five stencil points on the fly,
+// writes the centre value into the OTHER p buffer (the old p is still being read by neighbouring blocks) and goes on with
+// A p. Same values, same order of operations per cell as k_cg_pupdate followed by k_cg_spmv: bit-identical results.
 template <typename Real>
 __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_group& grid, const CgMatrix<Real>& A,
-    Real* __restrict__ x, Real* __restrict__ r, Real* __restrict__ p, Real* __restrict__ Ap,
+    Real* __restrict__ x, Real* __restrict__ r, Real* p, Real* p_other, Real* __restrict__ Ap,
     Real* rr0, Real* rr1, Real* pApP, CgState* st, const Real sst, const int max_iters, Real* scratch)
 {
     const int nx = A.nx, ny = A.ny;
@@ -51,9 +55,12 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
         const Real rr = sum_partials(rrP[0], nb, scratch);
         if(blockIdx.x == 0 && threadIdx.x == 0) st->rr = (double) rr;
     }
+    Real* pc = p;                 // the current search direction
+    Real* pn = p_other;           // where the next one is written
+    Real beta = 0;
     for(int it = 0; it < max_iters; it++)
     {
-        // Ap = A p, partials of p.Ap (k_cg_spmv)
+        // [p = r + beta p of the previous iteration,] Ap = A p, partials of p.Ap (k_cg_pupdate + k_cg_spmv)
         Real acc = 0;
         for(int wi = blockIdx.x; wi < items; wi += nb)
         {
@@ -61,11 +68,19 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
             if(xx < nx)
             {
                 const size_t i = (size_t) xx + (size_t) y * (size_t) nx;
-                const Real v = cg_apply(A, p, xx, y);
+                Real pv, v;
+                if(it == 0) { pv = pc[i]; v = cg_apply(A, pc, xx, y); }
+                else
+                {
+                    pv = pf_fma(beta, pc[i], r[i]);
+                    pn[i] = pv;
+                    v = cg_apply_axpy(A, pc, r, beta, pv, xx, y, A.which == 0 ? A.factor[i] : (Real) 0);
+                }
                 Ap[i] = v;
-                acc = pf_fma(p[i], v, acc);
+                acc = pf_fma(pv, v, acc);
             }
         }
+        if(it > 0) { Real* t = pc; pc = pn; pn = t; }
         acc = block_sum(acc, scratch);
         if(threadIdx.x == 0) pApP[blockIdx.x] = acc;
         grid.sync();
@@ -76,7 +91,7 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
         acc = 0;
         for(size_t i = blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < N; i += (size_t) nb * CG_THREADS)
         {
-            x[i] = pf_fma(alpha, p[i], x[i]);
+            x[i] = pf_fma(alpha, pc[i], x[i]);
             const Real rv = pf_fma(-alpha, Ap[i], r[i]);
             r[i] = rv;
             acc = pf_fma(rv, rv, acc);
@@ -84,18 +99,15 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
         acc = block_sum(acc, scratch);
         if(threadIdx.x == 0) rrP[(it + 1) & 1][blockIdx.x] = acc;
         grid.sync();
-        // convergence test, beta, p = r + beta p (k_cg_pupdate)
+        // convergence test and beta (k_cg_pupdate's scalars); the vector update waits for the next SpMV
         const Real rr_new = sum_partials(rrP[(it + 1) & 1], nb, scratch);
         if(rr_new < sst)
         {
             if(blockIdx.x == 0 && threadIdx.x == 0) { st->rr = (double) rr_new; st->iters = it; st->done = 1; }
             break;                                                          // every block takes this branch together (identical sums)
         }
-        const Real beta = rr_new / (rr > epsilon ? rr : epsilon);
-        for(size_t i = blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < N; i += (size_t) nb * CG_THREADS)
-            p[i] = pf_fma(beta, p[i], r[i]);
+        beta = rr_new / (rr > epsilon ? rr : epsilon);
         if(blockIdx.x == 0 && threadIdx.x == 0) st->rr = (double) rr_new;
-        grid.sync();
     }
     grid.sync();        // nobody may still be reading the partials when the next phase overwrites them
 }
@@ -134,7 +146,7 @@ k_si_step_coop(const SiCoopArgs<Real> a)
         if(threadIdx.x == 0) a.rr0[blockIdx.x] = acc;
     }
     grid.sync();
-    coop_cg_iterations<Real>(grid, a.A_F, a.nF, a.r, a.p, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 0, a.sst_F, a.max_F, scratch);
+    coop_cg_iterations<Real>(grid, a.A_F, a.nF, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 0, a.sst_F, a.max_F, scratch);
 
     // b_T (simulation.cu:893-899) fused with the T solve's set-up
     {
@@ -158,7 +170,7 @@ k_si_step_coop(const SiCoopArgs<Real> a)
         if(threadIdx.x == 0) a.rr0[blockIdx.x] = acc;
     }
     grid.sync();
-    coop_cg_iterations<Real>(grid, a.A_U, a.nU, a.r, a.p, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 1, a.sst_U, a.max_U, scratch);
+    coop_cg_iterations<Real>(grid, a.A_U, a.nU, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 1, a.sst_U, a.max_U, scratch);
 }
 
 } // namespace pf

@@ -811,12 +811,12 @@ static int semi_implicit_step_coop_inst(pf_solver* s, const pf_params& p, const 
     const int blocks = cg_blocks(s, s->nx, s->ny);
     if(s->force_per_kernel_cg || (long long) s->coop_blocks_per_sm[slot] * s->sm_count < blocks) return PF_OK;
 
-    void* q[4];
-    for(int i = 0; i < 4; i++) if(int rc = get_scratch(s, 4 + i, &q[i])) return rc;     // the per-kernel path's factor, r, p, Ap slots
+    void* q[5];
+    for(int i = 0; i < 5; i++) if(int rc = get_scratch(s, 4 + i, &q[i])) return rc;     // the per-kernel path's factor, r, p, Ap slots + the second p buffer
     Real* P = (Real*) s->partials;
     SiCoopArgs<Real> a; memset(&a, 0, sizeof a);
     a.F = F; a.U = U; a.U_base = U_base; a.nF = nF; a.nU = nU;
-    a.factor = (Real*) q[0]; a.r = (Real*) q[1]; a.p = (Real*) q[2]; a.Ap = (Real*) q[3];
+    a.factor = (Real*) q[0]; a.r = (Real*) q[1]; a.p = (Real*) q[2]; a.Ap = (Real*) q[3]; a.p2 = (Real*) q[4];
     a.rr0 = P; a.rr1 = P + CG_MAX_BLOCKS; a.pAp = P + 2 * CG_MAX_BLOCKS;
     a.st = s->d_cg;
     a.A_F = make_matrix<Real>(p, 0, a.factor);
