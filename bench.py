@@ -39,12 +39,12 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def load_traffic(solver, dtype_name):
+def load_traffic(solver, dtype_name, size=2048):
     """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/traffic.json), or None."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(path):
         with open(path) as f:
-            return json.load(f).get(f"{solver}_{dtype_name}_2048")
+            return json.load(f).get(f"{solver}_{dtype_name}_{size}")
     return None
 
 
@@ -330,7 +330,7 @@ def run_cuda_arm(args):
         alg_per_cell = (4 + 10 * cg_per_step) * rs
         achieved = alg_per_cell * cells / (ms * 1e-3 / args.steps) / 1e9
         kernel_name = "k_si_prepare + k_cg_spmv/update/pupdate (whole step)"
-    traffic = load_traffic(args.solver, args.dtype) if world == 1 and not args.wide else None
+    traffic = load_traffic(args.solver, args.dtype, p.nx) if world == 1 and not args.wide and args.field == "seed" else None
 
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
     e2e_secs, h2d, d2h = time_e2e(runner, torch, e2e_steps, world, dist)
