@@ -108,3 +108,70 @@ def test_slab_runner_two_gpus_semi_implicit(tmp_path, bc):
     assert np.linalg.norm(got_F - wF) / np.linalg.norm(wF) <= 1e-10
     assert np.linalg.norm(got_U - wU) / np.linalg.norm(wU) <= 1e-10
     assert not np.array_equal(got_F, seeded_fields(nx, ny, kind="interface")[0])
+
+
+FULL_WORKER = r'''
+import os, sys, json, hashlib
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from bachelors_b200._abi import PF_F64
+from bachelors_b200.app import initial_of
+from bachelors_b200.config import read_config
+from bachelors_b200.distributed import SlabRunner
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+root, solver, n, steps, out = sys.argv[1], sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), sys.argv[5]
+cfg = read_config(os.path.join(root, "benchmark_configs", "config_%s_2048.ini" % solver), ["[simulation]\nscale = %g" % (n / 512.0)])
+p = cfg.params
+assert p.nx == n and p.ny == n
+r = SlabRunner(p, PF_F64, rank=rank, world=world, device=local)
+r.solver.init_fields(p, initial_of(cfg), r.F.data_ptr(), r.U.data_ptr())      # ghost rows included: no first exchange needed
+ts = [r.step() for _ in range(steps)]
+r.sync()
+f0 = r.solver.first_owned_row
+shas = [hashlib.sha256(t[f0:f0 + r.layout.ny_local].cpu().numpy().tobytes()).hexdigest() for t in (r.F, r.U)]
+json.dump({"y0": r.layout.y0, "rows": r.layout.ny_local, "sha": shas, "ts": ts}, open(os.path.join(out, "r%d.json" % rank), "w"))
+r.close()
+dist.barrier(); dist.destroy_process_group()
+'''
+
+
+@pytest.mark.parametrize("solver", ["explicit-rk4-adaptive"])
+def test_full_size_16384_slabs_equal_the_single_gpu_run(tmp_path, solver):
+    """BASELINE.json configs[4] at its full size: the synthetic 16384^2 adaptive run cut into y-slabs over every GPU of the box
+    gives, slab by slab, the SHA-256 of the single-GPU run of the same grid (fields and accepted step sizes)."""
+    import hashlib
+    from bachelors_b200.app import initial_of
+    from bachelors_b200.config import read_config
+    G = S.lib().pf_device_count()
+    G = 8 if G >= 8 else (4 if G >= 4 else (2 if G >= 2 else 1))
+    if G < 2:
+        pytest.skip("needs at least two GPUs")
+    n, steps = 16384, 3
+    script = tmp_path / "full_worker.py"
+    script.write_text(FULL_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % G, "--master-addr", "127.0.0.1",
+           "--master-port", "29547", str(script), ROOT, solver, str(n), str(steps), str(tmp_path)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, res.stderr[-3000:]
+    parts = [json.load(open(tmp_path / ("r%d.json" % r))) for r in range(G)]
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", "config_%s_2048.ini" % solver), ["[simulation]\nscale = %g" % (n / 512.0)])
+    p = cfg.params
+    with S.Solver(n, n, PF_F64) as s:
+        F, U, tF, tU = (s.field_alloc() for _ in range(4))
+        s.init_fields(p, initial_of(cfg), F, U)
+        q, t, ts = p.copy(), 0.0, []
+        for i in range(steps):
+            q.iter, q.time = i, t
+            info = s.step(q, F, U, tF, tU)
+            t += info.dt_advanced; ts.append(info.dt_advanced)
+            F, tF, U, tU = tF, F, tU, U
+        wF, wU = s.download(F), s.download(U)
+    assert wF.shape == (n, n) and wF.sum() > 0
+    for part in parts:
+        assert part["ts"] == ts
+        y0, rows = part["y0"], part["rows"]
+        assert hashlib.sha256(wF[y0:y0 + rows].tobytes()).hexdigest() == part["sha"][0]
+        assert hashlib.sha256(wU[y0:y0 + rows].tobytes()).hexdigest() == part["sha"][1]
+    assert sum(part["rows"] for part in parts) == n
