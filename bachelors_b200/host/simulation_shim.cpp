@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 #include "simulation.h"     // the reference's header
+#include "log.h"            // the reference's logger (declarations; main.cpp holds the implementation, main.cpp:1)
 #include "pf_solver.h"
 
 namespace {
@@ -137,6 +138,18 @@ double sim_step(Sim_Map F, Sim_Map U, Sim_Map* next_F, Sim_Map* next_U, Sim_Para
     pf_params p = to_pf_params(params);
     pf_step_info info;
     shim_check(s, pf_step(s, &p, F.data, U.data, next_F->data, next_U->data, &info), "pf_step");
+
+    if(params.do_prints)                                                  // the console lines of the reference's solvers
+    {
+        if(params.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE)            // simulation.cu:484-485
+            LOG("SOLVER", info.Phi_converged ? LOG_DEBUG : LOG_WARN, "rk4-adaptive %s in %i iters with error F:%e | U:%e | tau:%e",
+                info.Phi_converged ? "converged" : "diverged", (int) info.Phi_iters, info.Phi_error, info.T_error, info.dt_advanced);
+        if(params.solver == SOLVER_TYPE_SEMI_IMPLICIT)                    // simulation.cu:889-890, :907-908
+        {
+            LOG_DEBUG("SOLVER", "%lli F %s in %i iters with error %e\n", (long long) params.iter, info.Phi_converged ? "converged" : "diverged", (int) info.Phi_iters, info.Phi_error);
+            LOG_DEBUG("SOLVER", "%lli U %s in %i iters with error %e\n", (long long) params.iter, info.T_converged ? "converged" : "diverged", (int) info.T_iters, info.T_error);
+        }
+    }
 
     if(params.stats)
     {

@@ -33,6 +33,22 @@ build_sim () { # $1 = suffix, $2.. = extra defines
   rm -f "$OUT/ref_glue_$sfx.o"
 }
 
+# The drop-in check: this repository's simulation_shim.cpp (the replacement of the reference's simulation.cu) behind the
+# SAME glue and the reference's own simulation.h / log.h, linked against libpfsolver.so instead of the reference solver:
+#   libshim_sim_f64.so / libshim_sim_f32.so  - the reference's structs and entry points at run time, our kernels below.
+build_shim () { # $1 = suffix, $2.. = extra defines
+  local sfx=$1; shift
+  local shim="$HERE/../bachelors_b200/host/simulation_shim.cpp"
+  if [ "$OUT/libshim_sim_$sfx.so" -nt "$shim" ] && [ "$OUT/libshim_sim_$sfx.so" -nt "$HERE/ref_glue/ref_glue.cpp" ] \
+     && [ "$OUT/libshim_sim_$sfx.so" -nt "$HERE/../include/pf_solver.h" ]; then return; fi
+  g++ -std=c++17 -O2 -fPIC -w "$@" -iquote "$REF" -I"$HERE/../include" -c "$shim" -o "$OUT/shim_$sfx.o"
+  $NVCC $ARCH -std=c++17 -O2 -Xcompiler -fPIC -w "$@" -Xcompiler -iquote -Xcompiler "$REF" -I"$HERE/../include" \
+      -c "$HERE/ref_glue/ref_glue.cpp" -o "$OUT/shim_glue_$sfx.o"
+  g++ -shared -o "$OUT/libshim_sim_$sfx.so" "$OUT/shim_$sfx.o" "$OUT/shim_glue_$sfx.o" \
+      -L"$HERE/../bachelors_b200" -lpfsolver -L/usr/local/cuda/lib64 -lcudart -Wl,-rpath,'$ORIGIN/../../bachelors_b200'
+  rm -f "$OUT/shim_$sfx.o" "$OUT/shim_glue_$sfx.o"
+}
+
 # CPU CG program (fast)
 if [ ! "$OUT/libref_cg.so" -nt "$REF/cojugate_gradient.c" ]; then
   g++ -std=c++17 -O2 -w -fPIC -shared -Dmain=ref_cg_main -x c++ "$REF/cojugate_gradient.c" -o "$OUT/libref_cg.so"
@@ -41,5 +57,9 @@ fi
 
 build_sim f64 &
 build_sim f32 -DCUSTOM_SETTINGS -DUSE_FLOATS -DCOMPILE_SIMULATION &
+if [ -f "$HERE/../bachelors_b200/libpfsolver.so" ]; then
+  build_shim f64 &
+  build_shim f32 -DCUSTOM_SETTINGS -DUSE_FLOATS -DCOMPILE_SIMULATION &
+fi
 wait
 ls -la "$OUT"

@@ -20,12 +20,15 @@ _libs = {}
 _tmpdirs = []
 
 
-def lib_path(dtype):
-    return os.path.join(_REF_DIR, "libref_sim_f64.so" if dtype == PF_F64 else "libref_sim_f32.so")
+def lib_path(dtype, impl="ref"):
+    """impl = "ref": the unmodified reference solver; "shim": the same glue and reference headers over this repository's
+    bachelors_b200/host/simulation_shim.cpp + libpfsolver.so (the drop-in as the reference's host would link it)."""
+    assert impl in ("ref", "shim")
+    return os.path.join(_REF_DIR, "lib%s_sim_%s.so" % (impl, "f64" if dtype == PF_F64 else "f32"))
 
 
-def available(dtype=PF_F64):
-    return os.path.exists(lib_path(dtype))
+def available(dtype=PF_F64, impl="ref"):
+    return os.path.exists(lib_path(dtype, impl))
 
 
 def _declare(L):
@@ -43,14 +46,18 @@ def _declare(L):
     return L
 
 
-def load(dtype, fresh=False):
-    path = lib_path(dtype)
+def load(dtype, fresh=False, impl="ref"):
+    path = lib_path(dtype, impl)
     if not os.path.exists(path):
         raise FileNotFoundError(f"{path}: run oracle/build_ref.sh where /root/reference exists")
+    if impl == "shim":
+        # the shim resolves libpfsolver.so relative to its own location (rpath $ORIGIN/../../bachelors_b200): load it in place.
+        # Its adaptive step size lives in the pf_solver handle, not in a function static: no private copy needed.
+        fresh = False
     if not fresh:
-        if dtype not in _libs:
-            _libs[dtype] = _declare(C.CDLL(path))
-        return _libs[dtype]
+        if (dtype, impl) not in _libs:
+            _libs[(dtype, impl)] = _declare(C.CDLL(path))
+        return _libs[(dtype, impl)]
     d = tempfile.mkdtemp(prefix="refsim_")
     _tmpdirs.append(d)
     private = os.path.join(d, os.path.basename(path))
@@ -61,8 +68,8 @@ def load(dtype, fresh=False):
 class RefSim:
     """The reference's sim_realloc / sim_modify / sim_step behind numpy arrays of shape (ny, nx)."""
 
-    def __init__(self, dtype, nx, ny, fresh=False):
-        self.L = load(dtype, fresh)
+    def __init__(self, dtype, nx, ny, fresh=False, impl="ref"):
+        self.L = load(dtype, fresh, impl)
         self.dtype, self.nx, self.ny = dtype, nx, ny
         self.np_dtype = np.float64 if dtype == PF_F64 else np.float32
         assert self.L.ref_sizeof_real() == (8 if dtype == PF_F64 else 4)
