@@ -10,6 +10,8 @@ over the C-ABI, with the rows SURVEY section 8f puts around the stepping path:
   * optionally a PNG of Phi per snapshot through the colour-map kernel (the viewer's shader, gl.h:221-283).
 
     python -m bachelors_b200.app config.ini [more.ini ...] [--dtype f64|f32] [--png]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 -m bachelors_b200.app config.ini
+                                      (N GPUs of one box: y-slabs, one snapshot file written by all ranks; app_slabs.py)
 
 The file formats are the reference's, so the reference's `plot.py` reads the output unchanged.
 """
@@ -212,14 +214,30 @@ def main(argv=None):
     ap.add_argument("--set", action="append", default=[], metavar="'[section]\\nkey = value'", help="config override")
     a = ap.parse_args(argv)
     rc = 0
+    world = int(os.environ.get("WORLD_SIZE", "1")) if "RANK" in os.environ else 0
+    if world > 0:                                               # launched by torchrun: one process per GPU, y-slabs
+        import torch
+        import torch.distributed as dist
+        from .app_slabs import run_config_slabs
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank = int(os.environ.get("RANK", "0"))
     for path in a.configs:
         try:
-            out = run_config(path, PF_F64 if a.dtype == "f64" else PF_F32, a.device, overrides=a.set, png=a.png,
-                             log=lambda m: print("[app] " + m, flush=True))
-            print("[app] %s -> %s (%i iters, %i snapshots)" % (path, out["folder"], out["iters"], out["snapshots"]))
+            dtype = PF_F64 if a.dtype == "f64" else PF_F32
+            log = lambda m: print("[app] " + m, flush=True)
+            if world > 0:
+                out = run_config_slabs(path, dtype, overrides=a.set, log=log)
+            else:
+                out = run_config(path, dtype, a.device, overrides=a.set, png=a.png, log=log)
+            if rank == 0:
+                print("[app] %s -> %s (%i iters, %i snapshots)" % (path, out["folder"], out["iters"], out["snapshots"]))
         except Exception as e:                                  # main.cpp:253-258: log, skip to the next config
             print("[app] failed to run config '%s': %s" % (path, e), file=sys.stderr)
             rc = 1
+    if world > 0:
+        dist.destroy_process_group()
     return rc
 
 

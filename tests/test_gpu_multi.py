@@ -175,3 +175,44 @@ def test_full_size_16384_slabs_equal_the_single_gpu_run(tmp_path, solver):
         assert hashlib.sha256(wF[y0:y0 + rows].tobytes()).hexdigest() == part["sha"][0]
         assert hashlib.sha256(wU[y0:y0 + rows].tobytes()).hexdigest() == part["sha"][1]
     assert sum(part["rows"] for part in parts) == n
+
+
+# ---- the headless host on slabs (bachelors_b200/app_slabs.py) ---------------------------------------------------------------
+def run_app_under_torchrun(nproc, config, override, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % nproc, "--master-addr", "127.0.0.1",
+           "--master-port", str(port), "-m", "bachelors_b200.app", os.path.join(ROOT, "benchmark_configs", config), "--set", override]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return res.stdout
+
+
+@pytest.mark.parametrize("solver", ["explicit-rk4", "explicit-rk4-adaptive", "semi-implicit"])
+def test_headless_host_on_slabs_writes_the_single_gpu_files(tmp_path, solver):
+    """`torchrun -m bachelors_b200.app` on every GPU of the box (one process on a one-GPU box: the same code path with
+    world size 1) against the single-GPU host: same snapshot schedule, every maps_NNNN.bin byte for byte the same file
+    for the explicit solvers, within 1e-10 for the semi-implicit one; config.ini and stats.csv next to them."""
+    from bachelors_b200.app import run_config
+    n = min(S.lib().pf_device_count(), 8)
+    config = "config_%s_256.ini" % solver
+    over = "[simulation]\nstop_after = 0.0005\n[snapshot]\ntimes = 5\nfolder = %s"
+    (tmp_path / "one").mkdir(); (tmp_path / "many").mkdir()
+    one = run_config(os.path.join(ROOT, "benchmark_configs", config), PF_F64, overrides=[over % (tmp_path / "one")])
+    out = run_app_under_torchrun(n, config, over % (tmp_path / "many"), 29571)
+    assert "%i iters, %i snapshots" % (one["iters"], one["snapshots"]) in out
+    folders = os.listdir(tmp_path / "many")
+    assert len(folders) == 1                                          # all ranks agreed on one folder name
+    many = tmp_path / "many" / folders[0]
+    names = sorted(os.listdir(many))
+    assert names == sorted(os.listdir(one["folder"])) and "config.ini" in names and "stats.csv" in names
+    maps = [x for x in names if x.startswith("maps_")]
+    assert len(maps) == one["snapshots"] + 1
+    for name in maps:
+        a = open(os.path.join(one["folder"], name), "rb").read()
+        b = open(many / name, "rb").read()
+        assert len(a) == len(b)
+        if solver != "semi-implicit" or n == 1:
+            assert a == b, name
+        else:
+            assert a[:112] == b[:112]                                 # header: sizes, dx, dy, time, iter, names
+            fa, fb = np.frombuffer(a[112:]), np.frombuffer(b[112:])
+            assert np.linalg.norm(fa - fb) <= 1e-10 * np.linalg.norm(fa)

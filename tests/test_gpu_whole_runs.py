@@ -45,7 +45,7 @@ def cuda_run(p, F0, U0, stop, max_steps):
 
 
 @pytest.mark.parametrize("solver,size,iters", [("explicit", 128, 8000), ("explicit-rk4", 128, 8000), ("explicit-rk4-adaptive", 128, 8920),
-                                               ("explicit-rk4", 256, 8000)])
+                                               ("explicit-rk4", 256, 8000), ("explicit-rk4-adaptive", 256, 9521)])
 def test_whole_run_is_bit_identical_to_the_reference(solver, size, iters):
     if not ref_sim.available(PF_F64):
         pytest.skip("oracle/_ref not built")
