@@ -24,6 +24,8 @@ struct SiCoopArgs {
     Real* nF; Real* nU;                                  // y(n+1)
     Real* factor; Real* r; Real* p; Real* p2; Real* Ap;   // scratch fields (p2: the second buffer of the search direction)
     Real* rr0; Real* rr1; Real* pAp;                     // per-block partial sums (CG_MAX_BLOCKS each)
+    unsigned long long* ll;                              // flagged partial sums (GridSum below); NULL: grid.sync + the arrays above
+    unsigned ll_epoch;                                   // first epoch of this launch (never reused while the slots live)
     CgState* st;                                         // [0] Phi solve, [1] T solve
     CgMatrix<Real> A_F, A_U;
     KConsts<Real> k;
@@ -33,16 +35,133 @@ struct SiCoopArgs {
     Real L, dt_omg;                                      // b_T = T + L (Phi' - Phi) + dt (1 - gamma) T (simulation.cu:893-899)
 };
 
+// One sum over all blocks that is also the grid barrier between two phases.
+//
+// Plain form: store the block's partial, cooperative grid.sync(), every block re-reads all partials (sum_partials).
+// That is ~8 dependent trips to L2 per phase (drain the stores, the arrival atomic, the polling loop, the re-read),
+// and at <= 1024^2 those trips - not bytes, not flops - are most of a semi-implicit step.
+//
+// Flagged form (ll != NULL): the partial travels WITH its flag. A block publishes {value, epoch} into its own slot
+// (8-byte words: 32 bits of the value + the 32-bit epoch, two words for a double; an aligned 8-byte access is single-copy
+// atomic, so a reader never sees a value without its flag) after a __threadfence() that orders the block's field stores
+// before it. Block 0 polls all slots until they carry the current epoch, sums them in the fixed order of sum_partials and
+// publishes the result the same way into a result slot, on which one thread of every other block spins. Seeing the
+// result is the barrier, and the value arrives with it: no arrival atomics (592 on one address), no re-read of the
+// partials by every block. (Every block polling every slot - the barrier with one trip fewer - was measured too: the
+// 592^2 x 16 B of polling traffic per barrier made a 1024^2 step 305 us instead of 222.) Two slot sets alternate by epoch
+// parity: a block can publish epoch e + 2 only after it has seen the result of e + 1, which block 0 forms from slots
+// that every block writes only after it has seen the result of e, i.e. after block 0 has finished reading the slots of e.
+// The grid must be co-resident (cooperative launch), as for grid.sync(). Same values added in the same order:
+// bit-identical to the plain form (PF_SI_GRID_SYNC=1; tests/test_gpu_parity.py runs both).
+// Measured, one B200, fp64 us/step plain -> flagged: 1024^2 222 -> 214, 512^2 148 -> 142, 256^2 112 -> 92.
+// __threadfence() is a sequentially consistent fence (fence.sc.gpu); release / acquire is all the flag protocol needs
+__device__ __forceinline__ void ll_fence()
+{
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
+__device__ __forceinline__ void ll_store(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.volatile.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_load(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <typename Real>
+struct GridSum {
+    cooperative_groups::grid_group& grid;
+    unsigned long long* ll;
+    unsigned epoch;
+    int nb;
+    Real* scratch;
+
+    // block_val: this block's partial (valid in thread 0, as block_sum returns it); arr: the plain form's partial array
+    __device__ __forceinline__ Real operator()(Real block_val, Real* arr)
+    {
+        if(ll == nullptr)
+        {
+            if(threadIdx.x == 0) arr[blockIdx.x] = block_val;
+            grid.sync();
+            return sum_partials(arr, nb, scratch);
+        }
+        const unsigned e = epoch++;
+        const unsigned long long tag = (unsigned long long) e << 32;
+        unsigned long long* set = ll + (size_t)(e & 1u) * (2 * CG_MAX_BLOCKS);
+        if(threadIdx.x == 0)
+        {
+            ll_fence();                                                     // release: the block's field stores (ordered before by __syncthreads) first
+            if constexpr (sizeof(Real) == 8)
+            {
+                const unsigned long long bits = (unsigned long long) __double_as_longlong((double) block_val);
+                ll_store(set + 2 * blockIdx.x, tag | (bits & 0xffffffffull));
+                ll_store(set + 2 * blockIdx.x + 1, tag | (bits >> 32));
+            }
+            else ll_store(set + 2 * blockIdx.x, tag | (unsigned long long) __float_as_uint((float) block_val));
+        }
+        unsigned long long* out = ll + 4 * CG_MAX_BLOCKS + 2 * (e & 1u);    // behind the two slot sets
+        __shared__ Real bcast;
+        if(blockIdx.x == 0)
+        {
+            Real acc = 0;
+            for(int i = threadIdx.x; i < nb; i += CG_THREADS)
+            {
+                unsigned long long a;
+                do { a = ll_load(set + 2 * i); } while((unsigned)(a >> 32) != e);
+                if constexpr (sizeof(Real) == 8)
+                {
+                    unsigned long long b;
+                    do { b = ll_load(set + 2 * i + 1); } while((unsigned)(b >> 32) != e);
+                    acc += (Real) __longlong_as_double((long long)((b << 32) | (a & 0xffffffffull)));
+                }
+                else acc += (Real) __uint_as_float((unsigned) a);
+            }
+            acc = block_sum(acc, scratch);                                  // its __syncthreads orders the polls before thread 0's fence below
+            if(threadIdx.x == 0)
+            {
+                bcast = acc;
+                if constexpr (sizeof(Real) == 8)
+                {
+                    const unsigned long long bits = (unsigned long long) __double_as_longlong((double) acc);
+                    ll_store(out, tag | (bits & 0xffffffffull));
+                    ll_store(out + 1, tag | (bits >> 32));
+                }
+                else ll_store(out, tag | (unsigned long long) __float_as_uint((float) acc));
+            }
+        }
+        else if(threadIdx.x == 0)
+        {
+            unsigned long long a;
+            do { a = ll_load(out); } while((unsigned)(a >> 32) != e);
+            if constexpr (sizeof(Real) == 8)
+            {
+                unsigned long long b;
+                do { b = ll_load(out + 1); } while((unsigned)(b >> 32) != e);
+                bcast = (Real) __longlong_as_double((long long)((b << 32) | (a & 0xffffffffull)));
+            }
+            else bcast = (Real) __uint_as_float((unsigned) a);
+        }
+        if(threadIdx.x == 0) ll_fence();                                    // acquire: loads after the barrier see what was stored before the flags
+        __syncthreads();
+        const Real r = bcast;
+        __syncthreads();
+        return r;
+    }
+};
+
 // The CG iterations after r, p, x and the partials of r.r (in rr0) have been set up: reference simulation.cu:649-690.
 // Two grid barriers per iteration: the p update of iteration it (p = r + beta p, simulation.cu:676) is not a phase of its
 // own but is folded into the SpMV of iteration it + 1, which forms r + beta*p at the five stencil points on the fly,
 // writes the centre value into the OTHER p buffer (the old p is still being read by neighbouring blocks) and goes on with
 // A p. Same values, same order of operations per cell as k_cg_pupdate followed by k_cg_spmv: bit-identical results.
 template <typename Real>
-__device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_group& grid, const CgMatrix<Real>& A,
+__device__ __forceinline__ void coop_cg_iterations(GridSum<Real>& gsum, Real rr, const CgMatrix<Real>& A,
     Real* __restrict__ x, Real* __restrict__ r, Real* p, Real* p_other, Real* __restrict__ Ap,
     Real* rr0, Real* rr1, Real* pApP, CgState* st, const Real sst, const int max_iters, Real* scratch)
 {
+    // rr: r.r of the initial residual (the caller's GridSum after the set-up phase - also the barrier in front of the first SpMV)
     const int nx = A.nx, ny = A.ny;
     const size_t N = (size_t) nx * (size_t) ny;
     const int segs = (nx + CG_THREADS - 1) / CG_THREADS;
@@ -52,7 +171,6 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
     Real* rrP[2] = {rr0, rr1};
     if(max_iters <= 0)
     {
-        const Real rr = sum_partials(rrP[0], nb, scratch);
         if(blockIdx.x == 0 && threadIdx.x == 0) st->rr = (double) rr;
     }
     Real* pc = p;                 // the current search direction
@@ -82,11 +200,8 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
         }
         if(it > 0) { Real* t = pc; pc = pn; pn = t; }
         acc = block_sum(acc, scratch);
-        if(threadIdx.x == 0) pApP[blockIdx.x] = acc;
-        grid.sync();
+        const Real pAp = gsum(acc, pApP);
         // alpha, x += alpha p, r -= alpha Ap, partials of the new r.r (k_cg_update)
-        const Real rr = sum_partials(rrP[it & 1], nb, scratch);
-        const Real pAp = sum_partials(pApP, nb, scratch);
         const Real alpha = rr / (pAp > epsilon ? pAp : epsilon);
         acc = 0;
         for(size_t i = blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < N; i += (size_t) nb * CG_THREADS)
@@ -97,19 +212,21 @@ __device__ __forceinline__ void coop_cg_iterations(cooperative_groups::grid_grou
             acc = pf_fma(rv, rv, acc);
         }
         acc = block_sum(acc, scratch);
-        if(threadIdx.x == 0) rrP[(it + 1) & 1][blockIdx.x] = acc;
-        grid.sync();
         // convergence test and beta (k_cg_pupdate's scalars); the vector update waits for the next SpMV
-        const Real rr_new = sum_partials(rrP[(it + 1) & 1], nb, scratch);
+        const Real rr_new = gsum(acc, rrP[(it + 1) & 1]);
         if(rr_new < sst)
         {
             if(blockIdx.x == 0 && threadIdx.x == 0) { st->rr = (double) rr_new; st->iters = it; st->done = 1; }
             break;                                                          // every block takes this branch together (identical sums)
         }
         beta = rr_new / (rr > epsilon ? rr : epsilon);
+        rr = rr_new;                                                        // the same partials summed in the same order: what the next iteration would recompute
         if(blockIdx.x == 0 && threadIdx.x == 0) st->rr = (double) rr_new;
     }
-    grid.sync();        // nobody may still be reading the partials when the next phase overwrites them
+    // plain form: nobody may still be reading the partial arrays when the next phase overwrites them. (Flagged form: the slot
+    // sets alternate; and every block has finished its last SpMV - the only reader of other blocks' p and r - before its
+    // p.Ap flag, which everyone has seen: the next phase may overwrite r and p.)
+    if(gsum.ll == nullptr) gsum.grid.sync();
 }
 
 template <typename Real, bool ANISO>
@@ -122,6 +239,8 @@ k_si_step_coop(const SiCoopArgs<Real> a)
     const int segs = (nx + CG_THREADS - 1) / CG_THREADS;
     const int items = segs * ny;
     const int nb = (int) gridDim.x;
+    GridSum<Real> gsum{grid, a.ll, a.ll_epoch, nb, scratch};
+    Real rr_init;
 
     // phase 0: the prepare kernel (simulation.cu:800-870) fused with the Phi solve's set-up r = b_Phi - A_Phi Phi, p = r, x = Phi
     {
@@ -143,10 +262,9 @@ k_si_step_coop(const SiCoopArgs<Real> a)
             }
         }
         acc = block_sum(acc, scratch);
-        if(threadIdx.x == 0) a.rr0[blockIdx.x] = acc;
+        rr_init = gsum(acc, a.rr0);
     }
-    grid.sync();
-    coop_cg_iterations<Real>(grid, a.A_F, a.nF, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 0, a.sst_F, a.max_F, scratch);
+    coop_cg_iterations<Real>(gsum, rr_init, a.A_F, a.nF, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 0, a.sst_F, a.max_F, scratch);
 
     // b_T (simulation.cu:893-899) fused with the T solve's set-up
     {
@@ -167,10 +285,9 @@ k_si_step_coop(const SiCoopArgs<Real> a)
             }
         }
         acc = block_sum(acc, scratch);
-        if(threadIdx.x == 0) a.rr0[blockIdx.x] = acc;
+        rr_init = gsum(acc, a.rr0);
     }
-    grid.sync();
-    coop_cg_iterations<Real>(grid, a.A_U, a.nU, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 1, a.sst_U, a.max_U, scratch);
+    coop_cg_iterations<Real>(gsum, rr_init, a.A_U, a.nU, a.r, a.p, a.p2, a.Ap, a.rr0, a.rr1, a.pAp, a.st + 1, a.sst_U, a.max_U, scratch);
 }
 
 } // namespace pf

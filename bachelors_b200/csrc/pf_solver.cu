@@ -53,6 +53,10 @@ struct pf_solver {
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
     int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
+    unsigned long long* ll_slots = nullptr; // flagged partial sums of the cooperative semi-implicit step (pf_si_coop.cuh GridSum)
+    unsigned ll_epoch = 1;                  // next unused epoch (0 = the cleared slots)
+    bool plain_grid_sync = false;           // test hook (PF_SI_GRID_SYNC=1): cooperative grid.sync() + partial arrays instead of the flagged sums
+           // test hook (PF_SI_NO_RESIDENT=1): the cooperative step without shared-memory residency
     bool force_per_kernel_cg = false;       // test hook (PF_SI_PER_KERNEL=1): take the per-kernel CG path
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
@@ -175,9 +179,12 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     PF_CREATE_CUDA(cudaSetDevice(device));
     PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
     { const char* e = getenv("PF_SI_PER_KERNEL"); s->force_per_kernel_cg = e && e[0] == '1'; }   // test hook: see tests/test_gpu_parity.py
+    { const char* e = getenv("PF_SI_GRID_SYNC"); s->plain_grid_sync = e && e[0] == '1'; }
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
+    PF_CREATE_CUDA(cudaMalloc(&s->ll_slots, (4 * CG_MAX_BLOCKS + 4) * sizeof(unsigned long long)));   // GridSum: 2 sets x 2 words per block + 2 x 2 result words
+    PF_CREATE_CUDA(cudaMemset(s->ll_slots, 0, (4 * CG_MAX_BLOCKS + 4) * sizeof(unsigned long long)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_cg, 2 * sizeof(CgState)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_err, 2 * sizeof(unsigned long long)));
@@ -203,6 +210,7 @@ void pf_destroy(pf_solver* s)
     if(s->stream) cudaStreamSynchronize(s->stream);
     for(int i = 0; i < PF_SCRATCH_SLOTS; i++) if(s->scratch[i]) cudaFree(s->scratch[i]);
     if(s->partials) cudaFree(s->partials);
+    if(s->ll_slots) cudaFree(s->ll_slots);
     if(s->d_cg) cudaFree(s->d_cg);
     if(s->d_stats) cudaFree(s->d_stats);
     if(s->d_err) cudaFree(s->d_err);
@@ -828,6 +836,13 @@ static int semi_implicit_step_coop_inst(pf_solver* s, const pf_params& p, const 
     a.sst_U = (Real) p.T_tolerance * (Real) p.T_tolerance * (Real)(int) N;
     a.max_F = p.Phi_max_iters; a.max_U = p.T_max_iters;
     a.L = (Real) p.L; a.dt_omg = (Real) p.dt * (1 - (Real) p.gamma);
+    if(!s->plain_grid_sync)
+    {
+        a.ll = s->ll_slots; a.ll_epoch = s->ll_epoch;
+        const unsigned used_epochs = 2u * (1u + 2u * (unsigned) std::max(std::max(a.max_F, a.max_U), 0)) + 2u;   // one per GridSum call of the launch, at most
+        s->ll_epoch += used_epochs;
+        if(s->ll_epoch < used_epochs + 1u) s->ll_epoch = 1;                 // 32-bit wrap: start over (the slots then hold epochs far away)
+    }
     void* args[] = {&a};
     PF_CUDA(s, cudaLaunchCooperativeKernel((const void*) kern, dim3((unsigned) blocks), dim3(CG_THREADS), args, 0, s->stream));
     PF_LAUNCH_CHECK(s);

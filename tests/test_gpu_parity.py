@@ -410,15 +410,20 @@ def test_semi_implicit_1024_iteration_counts():
 
 
 @pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("size", [(300, 171), (512, 203), (1024, 1024), (256, 37)], ids=lambda s: "%dx%d" % s)
 @pytest.mark.parametrize("variant", ["neumann", "periodic_aniso", "dirichlet_theta_half", "corrector_loop"])
-def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, dtype, monkeypatch):
+def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dtype, monkeypatch):
     """The one-launch cooperative step (pf_si_coop.cuh) and the per-kernel CG path (PF_SI_PER_KERNEL=1, read at pf_create) share
-    decomposition, arithmetic and summation trees: fields, iteration counts and residuals must agree bit for bit."""
+    decomposition, arithmetic and summation trees: fields, iteration counts and residuals must agree bit for bit.
+    PF_SI_GRID_SYNC=1 replaces the flagged all-block sums of the cooperative step (GridSum, pf_si_coop.cuh) by grid.sync() +
+    partial arrays - a third identical run."""
     kw = dict(neumann=dict(),
               periodic_aniso=dict(Phi_boundary="periodic", T_boundary="periodic", S=0.3),
               dirichlet_theta_half=dict(Phi_boundary="dirichlet", T_boundary="dirichlet", gamma=0.5, do_corrector_guess=1),
               corrector_loop=dict(do_corrector_loop=1, corrector_max_iters=2))[variant]
-    nx, ny = 300, 171
+    nx, ny = size
+    if size == (1024, 1024) and variant not in ("neumann", "periodic_aniso"):
+        pytest.skip("full size: two variants are enough")
     p = default_params(solver="semi-implicit", nx=nx, ny=ny, L0=nx / 128.0, Phi_tolerance=1e-9, T_tolerance=1e-9, Phi_max_iters=30, T_max_iters=30, **kw)
     npdt = np.float64 if dtype == PF_F64 else np.float32
     F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
@@ -434,12 +439,17 @@ def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, dtype, m
             return s.download(F), s.download(U), infos, s.kernel_launches - launches0
 
     monkeypatch.delenv("PF_SI_PER_KERNEL", raising=False)
+    monkeypatch.delenv("PF_SI_GRID_SYNC", raising=False)
     cF, cU, cinfo, claunches = run()
+    monkeypatch.setenv("PF_SI_GRID_SYNC", "1")                          # cooperative grid.sync() + partial arrays instead of the flagged sums
+    gF_, gU_, ginfo, glaunches = run()
+    assert np.array_equal(cF, gF_) and np.array_equal(cU, gU_) and cinfo == ginfo and claunches == glaunches
     monkeypatch.setenv("PF_SI_PER_KERNEL", "1")
     kF, kU, kinfo, klaunches = run()
     assert np.array_equal(cF, kF) and np.array_equal(cU, kU)
     assert cinfo == kinfo, (cinfo, kinfo)
     assert claunches < klaunches / 10, (claunches, klaunches)          # the cooperative path really ran
+    assert max(i[0] for i in cinfo) >= 2                               # and the solves really iterated
 
 
 @pytest.mark.parametrize("solver,dtype,host_dtype", [("explicit-rk4", PF_F64, PF_F64), ("explicit", PF_F64, PF_F64), ("explicit-rk4", PF_F32, PF_F32),
