@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 
 from bachelors_b200 import solver as S
-from bachelors_b200._abi import PF_F64
+from bachelors_b200._abi import PF_F32, PF_F64
 from bachelors_b200.config import read_config
 from bachelors_b200.initial import make_initial_conditions
 from conftest import ROOT
@@ -22,8 +22,8 @@ from oracle import ref_sim
 pytestmark = pytest.mark.gpu
 
 
-def reference_run(p, F0, U0, stop, max_steps):
-    with ref_sim.RefSim(PF_F64, p.nx, p.ny, fresh=True) as ref:
+def reference_run(p, F0, U0, stop, max_steps, dtype=PF_F64):
+    with ref_sim.RefSim(dtype, p.nx, p.ny, fresh=True) as ref:
         ref.upload(F0, U0)
         q, t, it = p.copy(), 0.0, 0
         while not (stop - t < 1e-16) and it < max_steps:
@@ -35,8 +35,8 @@ def reference_run(p, F0, U0, stop, max_steps):
         return F, U, t, it, ref.warnings
 
 
-def cuda_run(p, F0, U0, stop, max_steps):
-    with S.Solver(p.nx, p.ny, PF_F64) as s:
+def cuda_run(p, F0, U0, stop, max_steps, dtype=PF_F64):
+    with S.Solver(p.nx, p.ny, dtype) as s:
         F, U, F2, U2 = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
         q = p.copy(); q.iter, q.time = 0, 0.0
         # pf_run's stop rule is `time + advanced >= stop_time`; the reference's is `stop - t < 1e-16` - the same for these runs
@@ -58,6 +58,23 @@ def test_whole_run_is_bit_identical_to_the_reference(solver, size, iters):
     assert gt == rt
     assert np.array_equal(gF, rF) and np.array_equal(gU, rU)
     assert gF.sum() > 2 * F0.sum()                                   # the crystal grew: the run is not a fixed point
+
+
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive"])
+def test_whole_fp32_run_is_bit_identical_to_the_fp32_reference_build(solver):
+    """Real = float (the reference's USE_FLOATS build, simulation.h:21-25): float rounding at every operation, and still
+    every bit of both fields after the whole run, the final time and the number of accepted steps agree."""
+    if not ref_sim.available(PF_F32):
+        pytest.skip("oracle/_ref not built")
+    over = ["[simulation]\nT_tolerance = 1e-5\nPhi_tolerance = 1e-5"] if solver == "explicit-rk4-adaptive" else []
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", "config_%s_128.ini" % solver), over)
+    p, stop = cfg.params, cfg.simul_stop_time
+    F0, U0 = make_initial_conditions(cfg, np.float32)
+    rF, rU, rt, rit, _ = reference_run(p, F0, U0, stop, 40000, PF_F32)
+    gF, gU, gt, git = cuda_run(p, F0, U0, stop, 40000, PF_F32)
+    assert rit == git and rit >= 1000 and gt == rt
+    assert gF.dtype == np.float32 and np.array_equal(gF, rF) and np.array_equal(gU, rU)
+    assert gF.sum() > 2 * F0.sum()
 
 
 def test_whole_semi_implicit_run_stays_within_tolerance_of_the_reference():
