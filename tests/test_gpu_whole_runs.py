@@ -7,6 +7,7 @@ solver - the number of accepted steps are identical (128^2: 8920 steps, the numb
 A100 run, benchmark_ellapsed_times.txt:6). Semi-implicit: rounding differences of the CG sums (different reduction tree)
 are carried through 8000 steps of interface growth: measured 7.9e-14 (Phi) / 8.6e-15 (T) rel-L2 at the end of the run;
 asserted: the 1e-10 of the single-step bar."""
+import hashlib
 import os
 
 import numpy as np
@@ -58,6 +59,10 @@ def test_whole_run_is_bit_identical_to_the_reference(solver, size, iters):
     assert gt == rt
     assert np.array_equal(gF, rF) and np.array_equal(gU, rU)
     assert gF.sum() > 2 * F0.sum()                                   # the crystal grew: the run is not a fixed point
+    if (solver, size) == ("explicit-rk4-adaptive", 128):
+        # ... and the CPU oracle's end state of the same run (pinned without a GPU in tests/test_oracle_cpu.py)
+        from test_oracle_cpu import WHOLE_RUN_ADAPTIVE_128 as W
+        assert gt.hex() == W["time"] and hashlib.sha256(gF.tobytes()).hexdigest() == W["F"] and hashlib.sha256(gU.tobytes()).hexdigest() == W["U"]
 
 
 @pytest.mark.parametrize("solver", ["explicit", "explicit-rk4", "explicit-rk4-adaptive"])
