@@ -172,7 +172,6 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     s->ghost_lo = slab->has_lo ? slab->ghost : 0;
     s->ghost_hi = slab->has_hi ? slab->ghost : 0;
     s->rows_alloc = s->ghost_lo + slab->ny_local + s->ghost_hi;
-    int rc = PF_OK;
     auto bail = [&](int code) { g_create_error = s->err; pf_destroy(s); return code; };
     #define PF_CREATE_CUDA(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
         fail(s, e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA); } } while(0)
@@ -192,7 +191,6 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_cg, 2 * sizeof(CgState)));
     PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
     #undef PF_CREATE_CUDA
-    (void) rc;
     *out = s;
     return PF_OK;
 }
