@@ -329,7 +329,8 @@ def run_cuda_arm(args):
         cg_per_step = runner.cg_iters_total / max(args.steps, 1)
         alg_per_cell = (4 + 10 * cg_per_step) * rs
         achieved = alg_per_cell * cells / (ms * 1e-3 / args.steps) / 1e9
-        kernel_name = "k_si_prepare + k_cg_spmv/update/pupdate (whole step)"
+        kernel_name = ("k_si_step_coop (whole step in one cooperative launch)" if world == 1
+                       else "k_si_prepare + k_cg_spmv/update/pupdate (whole step, phase API)")
     traffic = load_traffic(args.solver, args.dtype, p.nx) if world == 1 and not args.wide and args.field == "seed" else None
 
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
