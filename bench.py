@@ -160,9 +160,14 @@ def run_reference_arm(args):
         return 0
     dtype = PF_F64 if args.dtype == "f64" else PF_F32
     cfg, desc = workload(args, 1)
+    if world > 1:                                # the CUDA arm's workload at this N; the sample below is a window of the same cells (same dx, dy, seed)
+        desc = workload(args, world)[1]
     # bounded sample per step: a centred 724^2 window (1/8 of the 2048^2 cells, same dx/dy) so that K steps end within minutes
     w = 724
     from oracle.oracle import Oracle, lib as olib
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, and at N > 1 rank 0 is the
+    # only rank that works in this arm
+    olib().orc_set_threads(len(os.sched_getaffinity(0)))
     cores = olib().orc_max_threads()
     p, F, U = cpu_window(cfg, dtype, w)
     o = Oracle(dtype, p.nx, p.ny)
