@@ -140,6 +140,7 @@ def cpu_window(cfg, dtype, w):
 def cpu_port_rate(cfg, dtype, budget_s, max_steps, w=None):
     """Times oracle steps on the host cores. -> (GLUPS, cores, sample text)."""
     from oracle.oracle import Oracle, lib as olib
+    olib().orc_set_threads(len(os.sched_getaffinity(0)))      # every core this process may use, whatever OMP_NUM_THREADS says
     cores = olib().orc_max_threads()
     p, F, U = cpu_window(cfg, dtype, w)
     o = Oracle(dtype, p.nx, p.ny)
