@@ -60,6 +60,10 @@ def test_whole_run_is_bit_identical_to_the_reference(solver, size, iters):
     assert gt == rt
     assert np.array_equal(gF, rF) and np.array_equal(gU, rU)
     assert gF.sum() > 2 * F0.sum()                                   # the crystal grew: the run is not a fixed point
+    if size == 128 and solver in ("explicit", "explicit-rk4"):
+        from test_oracle_cpu import WHOLE_RUN_128
+        W = WHOLE_RUN_128[solver]
+        assert gt.hex() == W["time"] and hashlib.sha256(gF.tobytes()).hexdigest() == W["F"] and hashlib.sha256(gU.tobytes()).hexdigest() == W["U"]
     if (solver, size) == ("explicit-rk4-adaptive", 128):
         # ... and the CPU oracle's end state of the same run (pinned without a GPU in tests/test_oracle_cpu.py)
         from test_oracle_cpu import WHOLE_RUN_ADAPTIVE_128 as W

@@ -217,6 +217,26 @@ WHOLE_RUN_ADAPTIVE_128 = {"time": "0x1.47b1d1b9adf0ep-5",
                           "U": "eb09bd7b4b57df3c24466adfd9713710a34142384df23e36cee88ccd0cd829fd"}
 
 
+# the fixed-step solvers' whole 128^2 runs (8000 steps): end state of the CPU oracle = CUDA path = unmodified reference
+WHOLE_RUN_128 = {
+    "explicit": {"time": "0x1.47ae147ae14f4p-5",
+                 "F": "e5ddc9ca3c6649b27f6a52ced58ad3afbbc3d65a1388d84a11c1e77fb6547276",
+                 "U": "ca99d7f13cfbfa47bb22153387b1f2b555ba257de937774a02d3c2f6fc665688"},
+    "explicit-rk4": {"time": "0x1.47ae147ae14f4p-5",
+                     "F": "068559de0edf098baf05311d0d74dc58a88cce16b26233170b7e472b8ad17be9",
+                     "U": "1f43afdf361212caeee09b3636b6c7eeccdbb82ea6f7afab84e21ef9edb3a447"},
+}
+
+
+@pytest.mark.parametrize("solver", ["explicit", "explicit-rk4"])
+def test_whole_fixed_step_run_128_end_state(solver):
+    cfg = read_config(os.path.join(ROOT, "benchmark_configs", "config_%s_128.ini" % solver))
+    F, U, t, n = run_to_stop(cfg)
+    W = WHOLE_RUN_128[solver]
+    assert n == 8000 and t.hex() == W["time"]
+    assert hashlib.sha256(F.tobytes()).hexdigest() == W["F"] and hashlib.sha256(U.tobytes()).hexdigest() == W["U"]
+
+
 def test_adaptive_step_count_128_matches_published():
     """benchmark_ellapsed_times.txt:6 (A100) 8920 iters, :151 (other GPU) 8922 iters at 128^2."""
     cfg = read_config(os.path.join(ROOT, "benchmark_configs", "config_explicit-rk4-adaptive_128.ini"))
