@@ -372,7 +372,7 @@ def run_cuda_arm(args):
         line["cg_iterations_per_step"] = runner.cg_iters_total / args.steps
 
     if rank == 0 and world == 1 and not args.no_cpu:
-        v, cores, sample = cpu_port_rate(cfg, dtype, budget_s=args.cpu_budget, max_steps=40, w=None if not args.wide else 2048)
+        v, cores, sample = cpu_port_rate(cfg, dtype, budget_s=args.cpu_budget, max_steps=400, w=None if not args.wide else 2048)
         line["cpu_baseline"] = {"value": v, "unit": "1e9 cell updates/s", "cores": cores, "kind": "port", "sample": sample}
     if rank == 0 and world == 1 and not args.no_ref_gpu:
         ref = same_box_reference(cfg, dtype, args)
