@@ -149,8 +149,8 @@ __global__ void k_debug_values(const Real* __restrict__ F, const Real* __restric
     Real tx = bsample(U, x + 1, y, nx, ny, U_bound) - bsample(U, x - 1, y, nx, ny, U_bound);
     Real ty = bsample(U, x, y + 1, nx, ny, U_bound) - bsample(U, x, y - 1, nx, ny, U_bound);
     const size_t i = (size_t) x + (size_t) y * (size_t) nx;
-    grad_F[i] = (Real) pf_hypotf((float) gx, (float) gy);
-    grad_U[i] = (Real) pf_hypotf((float) tx, (float) ty);
+    grad_F[i] = (Real) pf_hypotf_bf<false>((float) gx, (float) gy);
+    grad_U[i] = (Real) pf_hypotf_bf<false>((float) tx, (float) ty);
     aniso[i] = aniso_g<Real>(k, gx, gy);
 }
 
@@ -174,7 +174,7 @@ __device__ __forceinline__ void si_prepare_cell(const Real* __restrict__ F, cons
     Real gx, gy;
     if(k.do_corrector_guess) { gx = (E_Phi - W_Phi) * k.one_over_2dx; gy = (N_Phi - S_Phi) * k.one_over_2dy; }
     else                     { gx = (E_Phi - W_Phi) / (2 * k.dx);     gy = (N_Phi - S_Phi) / (2 * k.dy); }
-    const Real grad_Phi_norm = (Real) pf_hypotf((float) gx, (float) gy);
+    const Real grad_Phi_norm = (Real) pf_hypotf_bf<false>((float) gx, (float) gy);
     Real gf0, k1;
     if(ANISO) { Real g = aniso_g<Real>(k, gx, gy); gf0 = g * f0; k1 = g * k.k1_factor; }
     else      { gf0 = f0; k1 = k.k1_factor; }

@@ -428,8 +428,8 @@ static int launch_tiled(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
 
 // ---- streaming kernel (pf_stream.cuh): launch geometry -------------------------------------------------
 // CTA = 4 warps (128 columns, 128 - 2*NST of them interior). Resident CTAs per SM by register budget:
-// Euler 8 (<= 64 registers), the multi-stage schemes 4 (<= 128 registers); skew 1 (measured faster than skew 2).
-enum { STREAM_WARPS = 4, STREAM_SK = 1 };
+// Euler 8 (<= 64 registers), the multi-stage schemes 4 (<= 128 registers).
+enum { STREAM_WARPS = 4 };
 template <int SCHEME, bool ANISO> struct StreamOcc { static constexpr int MINB = SCHEME == SCHEME_EULER ? (ANISO ? 6 : 8) : 4; };
 
 // Number of row chunks: every CTA marches down `chunk` rows plus a pipeline fill of ~(SK+1)(NST-1) rows, so few long
@@ -457,11 +457,11 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
 template <typename Real, int SCHEME, bool ANISO>
 static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
 {
-    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, SK = STREAM_SK, MINB = StreamOcc<SCHEME, ANISO>::MINB;
+    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, MINB = StreamOcc<SCHEME, ANISO>::MINB;
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
-    auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB, SK>;
-    const size_t smem = stream_smem_bytes<Real, SCHEME, W, SK>();
+    auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
+    const size_t smem = stream_smem_bytes<Real, SCHEME, W>();
     if(!(s->stream_attr_done & (1u << inst_bit)))
     {
         PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
@@ -471,7 +471,7 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     const int own_rows = a.own_y1 - a.own_y0;
     if(own_rows <= 0) return PF_OK;
     const int strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
-    const int nch = stream_chunks(s->sm_count, MINB, strips, own_rows, (SK + 1) * (NST - 1));
+    const int nch = stream_chunks(s->sm_count, MINB, strips, own_rows, StreamGeom<SCHEME>::FILL);
     a.chunk = (own_rows + nch - 1) / nch;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
     dim3 grid((unsigned) strips, (unsigned)((own_rows + a.chunk - 1) / a.chunk));

@@ -79,13 +79,13 @@ static void launch_tiled(const FusedArgs<Real>& a)
     kern<<<grid, block, smem>>>(a);
 }
 
-template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB, int SK>
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
 static void launch_stream(FusedArgs<Real> a, int nch)
 {
     const int chunk = (a.own_y1 - a.own_y0 + nch - 1) / nch;      // nch balanced chunks
     constexpr int NST = SchemeStages<SCHEME>::value, EWI = 32 * WARPS - 2 * NST;
-    const size_t smem = stream_smem_bytes<Real, SCHEME, WARPS, SK>();
-    auto kern = k_stream_step<Real, SCHEME, ANISO, WARPS, MINB, SK>;
+    const size_t smem = stream_smem_bytes<Real, SCHEME, WARPS>();
+    auto kern = k_stream_step<Real, SCHEME, ANISO, WARPS, MINB>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     a.chunk = chunk;
@@ -164,9 +164,13 @@ static void run_scheme(const char* sname, int nx, int ny, int reps, const std::v
     cudaFree(dF); cudaFree(dU); cudaFree(rF); cudaFree(rU); cudaFree(oF); cudaFree(oU); cudaFree(derr);
 }
 
-#define V(Real, SCHEME, ANISO, W, MB, SK, CH) Variant<Real>{ "stream w" #W " b" #MB " sk" #SK " nch" #CH, launch_stream<Real, SCHEME, ANISO, W, MB, SK>, CH }
+#define V(Real, SCHEME, ANISO, W, MB, CH) Variant<Real>{ "stream w" #W " b" #MB " nch" #CH, launch_stream<Real, SCHEME, ANISO, W, MB>, CH }
 
+#ifdef KB_VARIANTS_FILE
+#include KB_VARIANTS_FILE          // ad-hoc experiment lists: -DKB_VARIANTS_FILE='"/tmp/x.inc"'
+#else
 #include "kbench_variants.inc"
+#endif
 
 int main(int argc, char** argv)
 {
