@@ -143,7 +143,7 @@ def run_config(config_path, dtype=PF_F64, device=0, overrides=(), png=False, log
         end_reached = False
         collect = bool(cfg.app_collect_stats)
         batched = p.solver != SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not collect
-        last_stats_save = 0.0                                                   # never advanced by the reference (main.cpp:233 only)
+        last_stats_save = 0.0                                                   # app->last_stats_save: set by every collection (main.cpp:233)
         t0 = time.perf_counter()
 
         def save_due(t):
@@ -192,9 +192,10 @@ def run_config(config_path, dtype=PF_F64, device=0, overrides=(), png=False, log
             else:
                 info = sol.step(params, F, U, F2, U2)
                 sim_time += info.dt_advanced
-                if collect and sim_time >= last_stats_save + cfg.app_collect_stats_every:
+                if collect and sim_time >= last_stats_save + cfg.app_collect_stats_every:      # main.cpp:554-555
                     step_res_count[0] = max(step_res_count[0], info.step_res_count)
                     stats_rows.append(_stats_row(params, info))
+                    last_stats_save = sim_time                                             # main.cpp:233
                 F, U, F2, U2 = F2, U2, F, U
                 it += 1
         sol.sync()

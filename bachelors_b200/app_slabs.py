@@ -138,15 +138,18 @@ def run_config_slabs(config_path, dtype=PF_F64, overrides=(), log=None, init_tim
             if end_reached:
                 break
             runner.time, runner.iter = sim_time, it
+            step_time = sim_time                                                # params.time of the step: what the reference's stats record
             sim_time += runner.step()
-            if collect and rank == 0 and sim_time >= last_stats_save + cfg.app_collect_stats_every:
-                # iteration counts only: the delta norms of the reference's stats (simulation.cu:1126-1142) are per-grid sums this
-                # host does not reduce across ranks
-                row = pf_stats_row()
-                row.time, row.iter = sim_time, it
-                cg = getattr(runner, "last_cg_iters", None)
-                row.Phi_iters, row.T_iters = cg if cg else (runner.last_attempts, runner.last_attempts)
-                stats_rows.append(row)
+            if collect and sim_time >= last_stats_save + cfg.app_collect_stats_every:     # main.cpp:554-555 (every rank keeps the same clock)
+                last_stats_save = sim_time                                                 # main.cpp:233
+                if rank == 0:
+                    # iteration counts only: the delta norms of the reference's stats (simulation.cu:1126-1142) are per-grid sums
+                    # this host does not reduce across ranks
+                    row = pf_stats_row()
+                    row.time, row.iter = step_time, it
+                    cg = getattr(runner, "last_cg_iters", None)
+                    row.Phi_iters, row.T_iters = cg if cg else (runner.last_attempts, runner.last_attempts)
+                    stats_rows.append(row)
             it += 1
         runner.sync()
         writer.finish()

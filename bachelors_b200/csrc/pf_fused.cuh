@@ -37,7 +37,8 @@ struct FusedArgs {
     int own_y0, own_y1;                // global rows this launch must produce
     int bc;                            // boundary type of both fields
     int wrap_y;                        // single GPU + periodic: wrap rows modulo ny_global
-    int chunk;                         // streaming kernel (pf_stream.cuh): rows produced per CTA
+    int strips, nch;                   // streaming kernel (pf_stream.cuh): column strips x row chunks = work units; chunk c produces rows
+                                       // own_y0 + [rows*c/nch, rows*(c+1)/nch) (balanced: lengths differ by at most one row)
     KConsts<Real> k;
     // scheme weights, computed on the host in Real arithmetic exactly as the reference does:
     //  RK4 (simulation.cu:330-337):  w[0]=dt/2 w[1]=dt/2 w[2]=dt w[3]=dt/6

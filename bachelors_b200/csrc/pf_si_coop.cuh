@@ -52,7 +52,7 @@ struct SiCoopArgs {
 // parity: a block can publish epoch e + 2 only after it has seen the result of e + 1, which block 0 forms from slots
 // that every block writes only after it has seen the result of e, i.e. after block 0 has finished reading the slots of e.
 // The grid must be co-resident (cooperative launch), as for grid.sync(). Same values added in the same order:
-// bit-identical to the plain form (PF_SI_GRID_SYNC=1; tests/test_gpu_parity.py runs both).
+// bit-identical to the plain form (pf_set_option PF_OPT_SI_GRID_SYNC; tests/test_gpu_parity.py runs both).
 // Measured, one B200, fp64 us/step plain -> flagged: 1024^2 222 -> 214, 512^2 148 -> 142, 256^2 112 -> 92.
 // __threadfence() is a sequentially consistent fence (fence.sc.gpu); release / acquire is all the flag protocol needs
 __device__ __forceinline__ void ll_fence()
@@ -118,9 +118,12 @@ struct GridSum {
                 }
                 else acc += (Real) __uint_as_float((unsigned) a);
             }
-            acc = block_sum(acc, scratch);                                  // its __syncthreads orders the polls before thread 0's fence below
+            acc = block_sum(acc, scratch);                                  // its __syncthreads orders all threads' polls before thread 0's fence
             if(threadIdx.x == 0)
             {
+                // acquire the partial flags, release the result: block B's field stores -> B's flag -> (this fence) -> result flag
+                // -> block C's acquire is then a chain of release/acquire pairs in the PTX memory model, not a hardware property
+                ll_fence();
                 bcast = acc;
                 if constexpr (sizeof(Real) == 8)
                 {

@@ -55,9 +55,9 @@ struct pf_solver {
     int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
     unsigned long long* ll_slots = nullptr; // flagged partial sums of the cooperative semi-implicit step (pf_si_coop.cuh GridSum)
     unsigned ll_epoch = 1;                  // next unused epoch (0 = the cleared slots)
-    bool plain_grid_sync = false;           // test hook (PF_SI_GRID_SYNC=1): cooperative grid.sync() + partial arrays instead of the flagged sums
-           // test hook (PF_SI_NO_RESIDENT=1): the cooperative step without shared-memory residency
-    bool force_per_kernel_cg = false;       // test hook (PF_SI_PER_KERNEL=1): take the per-kernel CG path
+    bool plain_grid_sync = false;           // PF_OPT_SI_GRID_SYNC: cooperative grid.sync() + partial arrays instead of the flagged sums
+    bool force_per_kernel_cg = false;       // PF_OPT_SI_PER_KERNEL: take the per-kernel CG path
+    int host_bands = 8;                     // PF_OPT_HOST_BANDS: row bands of the pipelined pf_step_host
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
     int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
@@ -162,6 +162,10 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     if((long long) nx * (long long) ny_global > 0x7fffffffLL) return fail(nullptr, PF_ERR_INVALID, "pf_create: nx*ny exceeds int32 (the reference's csize, cuda_util.cuh:19)");
     if(!slab || slab->ny_local <= 0 || slab->y0 < 0 || slab->y0 + slab->ny_local > ny_global || slab->ghost < 0)
         return fail(nullptr, PF_ERR_INVALID, "pf_create: bad slab");
+    // a neighbour's ghost rows are filled from this slab's first / last `ghost` OWNED rows (pf_halo_region): thinner slabs
+    // would need rows from two ranks away
+    if((slab->has_lo || slab->has_hi) && slab->ny_local < slab->ghost)
+        return fail(nullptr, PF_ERR_INVALID, "pf_create: a slab with a neighbour owns %d rows, fewer than its ghost depth %d", slab->ny_local, slab->ghost);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if(e != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(nullptr, PF_ERR_NO_DEVICE, "no CUDA device: %s (this library has no CPU fallback)", cudaGetErrorString(e)); }
@@ -177,8 +181,6 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
         fail(s, e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); return bail(e_ == cudaErrorMemoryAllocation ? PF_ERR_OOM : PF_ERR_CUDA); } } while(0)
     PF_CREATE_CUDA(cudaSetDevice(device));
     PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
-    { const char* e = getenv("PF_SI_PER_KERNEL"); s->force_per_kernel_cg = e && e[0] == '1'; }   // test hook: see tests/test_gpu_parity.py
-    { const char* e = getenv("PF_SI_GRID_SYNC"); s->plain_grid_sync = e && e[0] == '1'; }
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
     PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
@@ -233,6 +235,18 @@ void pf_destroy(pf_solver* s)
     if(s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
+}
+
+int pf_set_option(pf_solver* s, int option, int value)
+{
+    if(!s) return PF_ERR_INVALID;
+    switch(option)
+    {
+        case PF_OPT_HOST_BANDS:    if(value < 1) return fail(s, PF_ERR_INVALID, "PF_OPT_HOST_BANDS: %d", value); s->host_bands = value; return PF_OK;
+        case PF_OPT_SI_PER_KERNEL: s->force_per_kernel_cg = value != 0; return PF_OK;
+        case PF_OPT_SI_GRID_SYNC:  s->plain_grid_sync = value != 0; return PF_OK;
+        default: return fail(s, PF_ERR_INVALID, "pf_set_option: unknown option %d", option);
+    }
 }
 
 int pf_reset_state(pf_solver* s)
@@ -432,7 +446,7 @@ static int launch_tiled(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
 enum { STREAM_WARPS = 4 };
 template <int SCHEME, bool ANISO> struct StreamOcc { static constexpr int MINB = SCHEME == SCHEME_EULER ? (ANISO ? 6 : 8) : 4; };
 
-// Number of row chunks: every CTA marches down `chunk` rows plus a pipeline fill of ~(SK+1)(NST-1) rows, so few long
+// Number of row chunks: every CTA marches down its chunk plus a pipeline fill of 2(NST-1) rows, so few long
 // chunks waste the least work, but the grid should fill the machine's resident-CTA slots in whole waves. Cost model
 // (fitted to kbench runs on B200): a wave costs iterations x (a + b x resident CTAs per SM).
 static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
@@ -443,13 +457,12 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
     for(int n = 1; n <= max_n; n++)
     {
         const int chunk = (rows + n - 1) / n;
-        const int nch = (rows + chunk - 1) / chunk;
-        const long long ctas = (long long) strips * nch;
+        const long long ctas = (long long) strips * n;
         const long long full = ctas / slots, rest = ctas % slots;
         const double its = chunk + fill + 3.0;                       // the checked first/last groups run slower
         const double occ_rest = std::min<double>(minb, std::ceil((double) rest / sm_count));
         const double cost = its * (full * (0.6 + 0.145 * minb) + (rest ? 0.6 + 0.145 * occ_rest : 0.0));
-        if(cost < best) { best = cost; best_n = nch; }
+        if(cost < best) { best = cost; best_n = n; }
     }
     return best_n;
 }
@@ -470,12 +483,11 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     }
     const int own_rows = a.own_y1 - a.own_y0;
     if(own_rows <= 0) return PF_OK;
-    const int strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
-    const int nch = stream_chunks(s->sm_count, MINB, strips, own_rows, StreamGeom<SCHEME>::FILL);
-    a.chunk = (own_rows + nch - 1) / nch;
+    a.strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
+    a.nch = stream_chunks(s->sm_count, MINB, a.strips, own_rows, StreamGeom<SCHEME>::FILL);
+    const long long units = (long long) a.strips * a.nch;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
-    dim3 grid((unsigned) strips, (unsigned)((own_rows + a.chunk - 1) / a.chunk));
-    kern<<<grid, 32 * W, smem, stream>>>(a);
+    kern<<<(unsigned) units, 32 * W, smem, stream>>>(a);
     PF_LAUNCH_CHECK(s);
     return PF_OK;
 }
@@ -1133,21 +1145,31 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
     // 4: 2.06, 8: 1.94, 16: 2.16, 32: 2.55 per call - more bands shorten the pipeline fill but every copy and launch costs
     // host enqueue time; the two copy directions alone need 1.4 ms when overlapped.
     const int ny = s->ny;
-    int want_bands = 8;
-    if(const char* e = getenv("PF_HOST_BANDS")) want_bands = std::max(1, atoi(e));            // tuning hook
-    const int nb = std::max(1, std::min<int>({want_bands, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
+    const int nb = std::max(1, std::min<int>({s->host_bands, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
     const int rows_per = (ny + nb - 1) / nb;
     const size_t row_bytes = (size_t) s->nx * rs;
     // the copies must not overtake work already queued on the solver's stream that still reads or writes these fields
     PF_CUDA(s, cudaEventRecord(s->ev_host_begin, s->stream));
     PF_CUDA(s, cudaStreamWaitEvent(s->h2d_stream, s->ev_host_begin, 0));
+    // Periodic in y: band 0 also reads the LAST `ghost` rows of the grid (wrapped), which belong to the last band. They go up
+    // first, ahead of band 0, so that every band's inputs are on the device once the upload of the band after it is.
+    const int wrap_rows = params->Phi_boundary == PF_BOUNDARY_PERIODIC ? std::min(ny, pf_required_ghost(params->solver)) : 0;
+    if(wrap_rows)
+    {
+        const size_t off = (size_t)(ny - wrap_rows) * row_bytes, bytes = (size_t) wrap_rows * row_bytes;
+        PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+        PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+    }
     int bands = 0;
     for(int y0 = 0; y0 < ny; y0 += rows_per, bands++)
     {
-        const int y1 = std::min(ny, y0 + rows_per);
-        const size_t off = (size_t) y0 * row_bytes, bytes = (size_t)(y1 - y0) * row_bytes;
-        PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
-        PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+        const int y1 = std::min(ny - wrap_rows, y0 + rows_per);                 // the wrapped tail is already queued
+        const size_t off = (size_t) y0 * row_bytes, bytes = (size_t) std::max(0, y1 - y0) * row_bytes;
+        if(bytes)
+        {
+            PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+            PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
+        }
         PF_CUDA(s, cudaEventRecord(s->ev_up[bands], s->h2d_stream));
     }
     for(int b = 0; b < bands; b++)

@@ -82,12 +82,12 @@ struct StreamCtx {
     using V2 = typename Vec2T<Real>::type;
     V2* ybuf;                          // ring of canon y rows, offset to this thread's slot
     V2* cbuf;                          // U-deep ring of the stage-input rows of stages 2..NST, offset to this thread's slot
-    size_t lx;                         // clamped / wrapped column for loads
-    size_t out_off;                    // gx - row0*nx: added to row*nx for the stores
+    unsigned lx;                       // clamped / wrapped column for loads
+    unsigned gxu;                      // this thread's column (stores; only used where st_ok)
     bool wr_self;                      // this thread publishes its own values (false for the column just outside a non-periodic edge)
     bool x_lo_edge, x_hi_edge;         // non-periodic domain edge columns: they publish the ghost pair for the column outside
     bool st_ok;                        // this thread's column is an interior column inside the domain
-    bool edge_cta;                     // block-uniform: some thread of this CTA is a domain edge column
+    bool edge_warp;                    // warp-uniform: some thread of this warp is a non-periodic domain edge column
     int G0;                            // global row of stage 1 in iteration 0
     int Y0, Y1;                        // rows this CTA produces
     int ylo, yhi;                      // rows a stage may be evaluated on (domain rows; everything when periodic)
@@ -104,7 +104,8 @@ __device__ __forceinline__ void stream_store_pair(typename Vec2T<Real>::type* p,
 template <typename Real>
 __device__ __forceinline__ void stream_store_ghost(const FusedArgs<Real>& a, const StreamCtx<Real>& c, typename Vec2T<Real>::type* p, const Real vF, const Real vT)
 {
-    typename Vec2T<Real>::type g; g.x = ghost_of(vF, a.bc); g.y = ghost_of(vT, a.bc);
+    typename Vec2T<Real>::type g; g.x = vF; g.y = vT;
+    if(a.bc == PF_BOUNDARY_DIRICHLET_ZERO) { g.x = (Real) 0 - vF; g.y = (Real) 0 - vT; }      // uniform branch; Neumann repeats the edge cell
     if(c.x_lo_edge) p[-1] = g;
     if(c.x_hi_edge) p[+1] = g;
 }
@@ -224,9 +225,11 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
         }
         // keep the last stage in the straight-line code of the row (the halo threads compute it too, only the store is predicated)
         keep_here(nF, nT);
+        // element indices fit 32 bits (pf_create checks nx*ny); predicated stores instead of a branch keep the row one basic block
+        // A branch, not predicated stores (measured: predicated st.global costs 2-4 %). Element indices fit 32 bits (pf_create).
         if(c.st_ok)
         {
-            const size_t idx = (size_t) row * (size_t) a.nx + c.out_off;
+            const unsigned idx = (unsigned)(row - a.row0) * (unsigned) a.nx + c.gxu;
             a.out_F[idx] = nF;
             a.out_U[idx] = nT;
         }
@@ -247,15 +250,15 @@ struct StreamStages {
 // Local memory row of global row g: wrapped (single GPU, periodic) or clamped into the rows that exist locally and
 // in the domain, so that loads of rows that only feed garbage stay inside the allocation.
 template <typename Real>
-__device__ __forceinline__ size_t stream_mem_row(const FusedArgs<Real>& a, int g, const int rlo, const int rhi)
+__device__ __forceinline__ unsigned stream_mem_row(const FusedArgs<Real>& a, int g, const int rlo, const int rhi)
 {
     if(a.wrap_y) { while(g < 0) g += a.ny_global; while(g >= a.ny_global) g -= a.ny_global; }
     g = g < rlo ? rlo : (g > rhi ? rhi : g);
-    return (size_t)(g - a.row0);
+    return (unsigned)(g - a.row0);
 }
 
 // One row of the march. PH = it mod U.
-template <typename Real, int SCHEME, bool ANISO, int EW, bool CHECKED, int PH>
+template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool CHECKED, int PH>
 __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                  const int it, const int rlo, const int rhi)
 {
@@ -265,12 +268,12 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
     constexpr int j1 = pmod(PH + 1, U), j2 = pmod(PH + 2, U);
     const int g1 = c.G0 + it;
     // 1. prefetch the raw y of row g1 + 2, retired at the end of this iteration
-    const size_t ro = (CHECKED ? stream_mem_row(a, g1 + 1 + 1, rlo, rhi) : (size_t)(g1 + 1 + 1 - a.row0)) * (size_t) a.nx + c.lx;
+    const unsigned ro = (CHECKED ? stream_mem_row(a, g1 + 1 + 1, rlo, rhi) : (unsigned)(g1 + 1 + 1 - a.row0)) * (unsigned) a.nx + c.lx;
     const Real tF = a.F[ro], tT = a.U[ro];
     if(!CHECKED && g1 + 2 + G::L2_AHEAD <= rhi)
     {
         // pull the rows this CTA reads a few iterations from now into L2 (measured: -1.5 % on the RK4 step at 2048^2)
-        const size_t po = ro + (size_t) G::L2_AHEAD * (size_t) a.nx;
+        const unsigned po = ro + (unsigned) G::L2_AHEAD * (unsigned) a.nx;
         asm volatile("prefetch.global.L2 [%0];" :: "l"(a.F + po));
         asm volatile("prefetch.global.L2 [%0];" :: "l"(a.U + po));
     }
@@ -282,8 +285,10 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
         const StreamState<Real, SCHEME> old = st;
         StreamStages<Real, SCHEME, ANISO, EW, CHECKED, PH, 1>::run(a, c, old, st, it);
     }
-    // 3b. CTAs that hold a non-periodic domain edge column: the ghost pairs of everything published in this row
-    if(c.edge_cta)
+    // 3b. strips with a non-periodic domain edge column (EDGE), in the warp that holds it: the ghost pairs of everything
+    // published in this row. The other strips run an instantiation without this block: its mere presence (a branch that cuts
+    // the row's basic block in two) costs every CTA 6 % (measured, profiles/r02_cta_balance.md).
+    if(EDGE && c.edge_warp)
     {
         stream_store_ghost<Real>(a, c, ypub, st.yF[j1], st.yT[j1]);
         #pragma unroll
@@ -299,14 +304,14 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
     __syncthreads();
 }
 
-template <typename Real, int SCHEME, bool ANISO, int EW, bool CHECKED, int PH>
+template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool CHECKED, int PH>
 struct StreamIters {
     static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                const int it0, const int rlo, const int rhi)
     {
-        stream_iteration<Real, SCHEME, ANISO, EW, CHECKED, PH>(a, c, st, it0 + PH, rlo, rhi);
+        stream_iteration<Real, SCHEME, ANISO, EW, EDGE, CHECKED, PH>(a, c, st, it0 + PH, rlo, rhi);
         if constexpr (PH + 1 < StreamGeom<SCHEME>::U)
-            StreamIters<Real, SCHEME, ANISO, EW, CHECKED, PH + 1>::run(a, c, st, it0, rlo, rhi);
+            StreamIters<Real, SCHEME, ANISO, EW, EDGE, CHECKED, PH + 1>::run(a, c, st, it0, rlo, rhi);
     }
 };
 
@@ -325,6 +330,8 @@ constexpr size_t stream_smem_bytes()
     return sizeof(typename Vec2T<Real>::type) * (size_t)(G::YR + G::U * (G::NST - 1)) * (32 * WARPS + 2);
 }
 
+// Work decomposition: a CTA = one unit (1-D grid) = a strip of EW columns x a chunk of rows; the chunks of a strip are
+// balanced (lengths differ by at most one row).
 template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB)
 k_stream_step(const FusedArgs<Real> a)
@@ -333,38 +340,48 @@ k_stream_step(const FusedArgs<Real> a)
     using G = StreamGeom<SCHEME>;
     constexpr int NST = G::NST, U = G::U;
     constexpr int H = NST, EW = 32 * WARPS, EWI = EW - 2 * H, ROWSTRIDE = EW + 2;
+    constexpr int RING_ELEMS = (G::YR + U * (NST - 1)) * ROWSTRIDE;
     extern __shared__ __align__(16) unsigned char pf_smem_raw[];
     V2* const smem = reinterpret_cast<V2*>(pf_smem_raw);
+    const int cx = (int) threadIdx.x;
 
     const int nx = a.nx, NY = a.ny_global;
     const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
+    const int own_rows = a.own_y1 - a.own_y0;
+    // units in dispatch order: the two edge strips of a non-periodic grid first (their CTAs do a little more per row, and
+    // the CTAs dispatched first get the SM's oldest, i.e. fastest, resident slot), then the interior strips
+    const int unit = (int) blockIdx.x;
+    int strip, chunk;
+    if(periodic || a.strips < 3) { strip = unit % a.strips; chunk = unit / a.strips; }
+    else if(unit < 2 * a.nch)    { strip = (unit & 1) ? a.strips - 1 : 0; chunk = unit >> 1; }
+    else                         { const int v = unit - 2 * a.nch; strip = 1 + v % (a.strips - 2); chunk = v / (a.strips - 2); }
 
     StreamCtx<Real> c;
-    const int cx = threadIdx.x;
     // Periodic: strip k owns columns [k*EWI, (k+1)*EWI), its threads start H columns to the left (wrapped).
     // Non-periodic: nothing outside the domain is needed (the edge thread publishes the ghost pair itself), so thread 0 of
     // strip 0 IS column 0, and every column of the first / last strip up to the domain edge is clean:
     // strip k owns [k*EWI + (k ? H : 0), (k+1)*EWI + H), the last one everything up to nx - 1 (see stream_strips).
-    const int gx0 = (int) blockIdx.x * EWI - (periodic ? H : 0);       // column of thread 0
+    const int gx0 = strip * EWI - (periodic ? H : 0);                  // column of thread 0
     const int gx = gx0 + cx;
-    if(periodic) { int lx = gx % nx; if(lx < 0) lx += nx; c.lx = (size_t) lx; }
-    else         c.lx = (size_t)(gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx));
+    if(periodic) { int lx = gx % nx; if(lx < 0) lx += nx; c.lx = (unsigned) lx; }
+    else         c.lx = (unsigned)(gx < 0 ? 0 : (gx >= nx ? nx - 1 : gx));
     c.x_lo_edge = !periodic && gx == 0;
     c.x_hi_edge = !periodic && gx == nx - 1;
     c.wr_self = periodic || (gx != -1 && gx != nx);
-    const int cx_lo = (!periodic && gx0 == 0) ? 0 : H;                  // left domain edge inside the CTA: no garbage enters from the left
-    const int cx_hi = (!periodic && gx0 + EW >= nx) ? EW : EW - H;      // right domain edge inside the CTA: none from the right
+    const int cx_lo = (!periodic && gx0 == 0) ? 0 : H;                  // left domain edge inside the strip: no garbage enters from the left
+    const int cx_hi = (!periodic && gx0 + EW >= nx) ? EW : EW - H;      // right domain edge inside the strip: none from the right
     c.st_ok = cx >= cx_lo && cx < cx_hi && gx < nx;
-    c.edge_cta = !periodic && (gx0 <= 0 || gx0 + EW >= nx);
-    c.out_off = (size_t)((long long) gx - (long long) a.row0 * (long long) nx);
-    c.Y0 = a.own_y0 + (int) blockIdx.y * a.chunk;
-    c.Y1 = min(c.Y0 + a.chunk, a.own_y1);
+    c.edge_warp = __any_sync(0xffffffffu, c.x_lo_edge || c.x_hi_edge);
+    const bool edge_strip = !periodic && (gx0 <= 0 || gx0 + EW >= nx);      // block-uniform
+    c.gxu = (unsigned) gx;
+    c.Y0 = a.own_y0 + (int)((long long) own_rows * chunk / a.nch);
+    c.Y1 = a.own_y0 + (int)((long long) own_rows * (chunk + 1) / a.nch);
+    const int n_it = (c.Y1 - c.Y0) + G::FILL;
     c.G0 = c.Y0 - (NST - 1);
     c.ylo = periodic ? INT_MIN : 0;
     c.yhi = periodic ? INT_MAX : NY;
     c.ybuf = smem + cx + 1;
     c.cbuf = smem + G::YR * ROWSTRIDE + cx + 1;
-    const int n_it = (c.Y1 - c.Y0) + G::FILL;
     // rows that exist both locally and in the domain (loads are clamped into them)
     const int rlo = periodic ? a.row0 : max(a.row0, 0);
     const int rhi = (periodic ? a.row0 + a.rows_local : min(a.row0 + a.rows_local, NY)) - 1;
@@ -386,11 +403,11 @@ k_stream_step(const FusedArgs<Real> a)
     st.negmask = 0; st.errF = 0; st.errT = 0;
 
     // zero the rings (pads included), then preload y rows G0-1, G0, G0+1
-    for(int i = threadIdx.x; i < (G::YR + U * (NST - 1)) * ROWSTRIDE; i += EW) { V2 z; z.x = 0; z.y = 0; smem[i] = z; }
+    for(int i = cx; i < RING_ELEMS; i += EW) { V2 z; z.x = 0; z.y = 0; smem[i] = z; }
     #pragma unroll
     for(int d = -1; d <= 1; d++)
     {
-        const size_t ro = stream_mem_row(a, c.G0 + d, rlo, rhi) * (size_t) nx + c.lx;
+        const unsigned ro = stream_mem_row(a, c.G0 + d, rlo, rhi) * (unsigned) nx + c.lx;
         const Real f = a.F[ro], u = a.U[ro];
         const int j = d < 0 ? U - 1 : d;
         st.yF[j] = canon_zero(f); st.yT[j] = canon_zero(u);
@@ -400,7 +417,7 @@ k_stream_step(const FusedArgs<Real> a)
     {
         V2* const ypub = c.ybuf + (c.G0 & (G::YR - 1)) * ROWSTRIDE;
         stream_store_pair<Real>(ypub, c.wr_self, st.yF[0], st.yT[0]);
-        if(c.edge_cta) stream_store_ghost<Real>(a, c, ypub, st.yF[0], st.yT[0]);
+        if(c.edge_warp) stream_store_ghost<Real>(a, c, ypub, st.yF[0], st.yT[0]);
     }
     __syncthreads();
 
@@ -410,16 +427,23 @@ k_stream_step(const FusedArgs<Real> a)
     int lo_it = max(G::FILL, rlo - 1 - 1 - c.G0);
     int hi_it = min((c.Y1 - c.Y0) + 2 * NST - 2, rhi - 1 - c.G0);
     if(!periodic) { lo_it = max(lo_it, 1 - c.G0 + (NST - 1)); hi_it = min(hi_it, NY - 1 - c.G0); }
-    for(int it0 = 0; it0 < n_it; it0 += U)
-    {
-        if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, false, 0>::run(a, c, st, it0, rlo, rhi);
-        else                                 StreamIters<Real, SCHEME, ANISO, EW, true, 0>::run(a, c, st, it0, rlo, rhi);
-    }
+    if(edge_strip)
+        for(int it0 = 0; it0 < n_it; it0 += U)
+        {
+            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, true, false, 0>::run(a, c, st, it0, rlo, rhi);
+            else                                 StreamIters<Real, SCHEME, ANISO, EW, true, true, 0>::run(a, c, st, it0, rlo, rhi);
+        }
+    else
+        for(int it0 = 0; it0 < n_it; it0 += U)
+        {
+            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, false, false, 0>::run(a, c, st, it0, rlo, rhi);
+            else                                 StreamIters<Real, SCHEME, ANISO, EW, false, true, 0>::run(a, c, st, it0, rlo, rhi);
+        }
 
     if(SCHEME == SCHEME_RKM)
     {
         const Real eF = warp_max(st.errF), eT = warp_max(st.errT);
-        if((threadIdx.x & 31) == 0)
+        if((cx & 31) == 0)
         {
             if(eF > 0) atomic_max_nonneg(a.err_bits + 0, eF);
             if(eT > 0) atomic_max_nonneg(a.err_bits + 1, eT);

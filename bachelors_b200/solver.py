@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libpfsolver.so")
 # every symbol include/pf_solver.h declares
 EXPORTS = [
     "pf_abi_version", "pf_device_count", "pf_last_error", "pf_sizeof_real", "pf_required_ghost",
-    "pf_create", "pf_create_slab", "pf_destroy", "pf_reset_state",
+    "pf_create", "pf_create_slab", "pf_destroy", "pf_reset_state", "pf_set_option",
     "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download", "pf_upload_raw", "pf_download_raw",
     "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
@@ -53,7 +53,7 @@ def lib():
         "pf_abi_version": (i32, []), "pf_device_count": (i32, []), "pf_last_error": (C.c_char_p, [vp]),
         "pf_sizeof_real": (sz, [i32]), "pf_required_ghost": (i32, [i32]),
         "pf_create": (i32, [P(vp), i32, i32, i32, i32]), "pf_create_slab": (i32, [P(vp), i32, i32, i32, i32, P(pf_slab)]),
-        "pf_destroy": (None, [vp]), "pf_reset_state": (i32, [vp]),
+        "pf_destroy": (None, [vp]), "pf_reset_state": (i32, [vp]), "pf_set_option": (i32, [vp, i32, i32]),
         "pf_field_alloc": (i32, [vp, P(vp)]), "pf_field_free": (i32, [vp, vp]), "pf_field_rows": (i32, [vp, P(i32), P(i32)]),
         "pf_upload": (i32, [vp, vp, vp, sz, i32]), "pf_download": (i32, [vp, vp, vp, sz, i32]),
         "pf_upload_raw": (i32, [vp, vp, vp, sz]), "pf_download_raw": (i32, [vp, vp, vp, sz]),
@@ -215,6 +215,9 @@ class Solver:
 
     def reset_state(self):
         self._ck(lib().pf_reset_state(self._h))
+
+    def set_option(self, option, value):
+        self._ck(lib().pf_set_option(self._h, option, int(value)))
 
     @property
     def stream(self):

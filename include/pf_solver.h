@@ -145,6 +145,13 @@ PF_API int  pf_create(pf_solver** out, int device, int dtype, int nx, int ny);
 PF_API int  pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global, const pf_slab* slab);
 PF_API void pf_destroy(pf_solver* s);
 PF_API int  pf_reset_state(pf_solver* s);                   /* forget adaptive tau / corrector parity (the reference needs a new process) */
+/* Tuning and diagnostic switches of one handle (the reference has compile-time #defines for such things, simulation.cu:103-109). */
+typedef enum pf_option {
+    PF_OPT_HOST_BANDS    = 0,  /* row bands of the pipelined pf_step_host (default 8, at most 32) */
+    PF_OPT_SI_PER_KERNEL = 1,  /* != 0: semi-implicit step through the per-kernel CG path instead of the one cooperative launch */
+    PF_OPT_SI_GRID_SYNC  = 2,  /* != 0: cooperative step with grid.sync() + partial arrays instead of the flagged all-block sums */
+} pf_option;
+PF_API int  pf_set_option(pf_solver* s, int option, int value);
 
 /* ---- fields: replaces sim_realloc (simulation.cu:88-101) ------------------------------------ */
 /* A field is a dense row-major array of rows_alloc x nx reals on the device, index x + y*nx

@@ -172,6 +172,27 @@ def test_headless_run_writes_the_reference_files(tmp_path, solver_name, dtype):
         assert np.array_equal(last["maps"]["F"], oF.astype(np.float64)) and np.array_equal(last["maps"]["U"], oU.astype(np.float64))
 
 
+def test_collect_stats_every_throttles_rows_like_the_reference(tmp_path):
+    """app_collect_stats sets last_stats_save = sim_time (main.cpp:233), so `collect_stats_every` > 0 leaves one row per
+    interval, not one per step; every row carries the time and iteration of the step's params (main.cpp:543-544)."""
+    every = 2.5e-5                                                               # 5 steps of dt = 5e-6
+    over = "[simulation]\nstop_after = 0.0002\n[snapshot]\ntimes = 4\nfolder = %s\n[program]\ncollect_stats = true\ncollect_stats_every = %g" % (tmp_path, every)
+    path = os.path.join(ROOT, "benchmark_configs", "config_explicit_128.ini")
+    out = run_config(path, PF_F64, overrides=[over])
+    cfg = read_config(path, [over])
+    # replay of the reference loop's test on the same additions of dt (main.cpp:553-555)
+    want, t, last = [], 0.0, 0.0
+    for it in range(out["iters"]):
+        t_step = t
+        t += cfg.params.dt
+        if t >= last + every:
+            want.append(it)
+            last = t
+        del t_step
+    lines = open(os.path.join(out["folder"], "stats.csv")).read().strip().split("\n")
+    assert [int(l.split(",")[1]) for l in lines[2:]] == want and 0 < len(want) < out["iters"]
+
+
 def test_full_size_adaptive_run_takes_the_published_number_of_steps(tmp_path):
     """the reference's adaptive solver needs 9522 steps (A100; 9523 on the other GPU) to t = 0.04 at
     2048^2 with tolerances 5e-9 (benchmark_ellapsed_times.txt:112,199). The whole run, 11 snapshots included."""

@@ -11,7 +11,8 @@ import numpy as np
 import pytest
 
 from bachelors_b200 import solver as S
-from bachelors_b200._abi import (PF_ERR_INVALID, PF_ERR_UNSUPPORTED, PF_F32, PF_F64, default_params, pf_slab)
+from bachelors_b200._abi import (PF_ERR_INVALID, PF_ERR_UNSUPPORTED, PF_F32, PF_F64, PF_OPT_HOST_BANDS, PF_OPT_SI_GRID_SYNC,
+                                 PF_OPT_SI_PER_KERNEL, default_params, pf_slab)
 from bachelors_b200.config import read_config
 from bachelors_b200.initial import make_initial_conditions
 from bachelors_b200.testing import seeded_fields
@@ -412,10 +413,10 @@ def test_semi_implicit_1024_iteration_counts():
 @pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
 @pytest.mark.parametrize("size", [(300, 171), (512, 203), (1024, 1024), (256, 37)], ids=lambda s: "%dx%d" % s)
 @pytest.mark.parametrize("variant", ["neumann", "periodic_aniso", "dirichlet_theta_half", "corrector_loop"])
-def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dtype, monkeypatch):
-    """The one-launch cooperative step (pf_si_coop.cuh) and the per-kernel CG path (PF_SI_PER_KERNEL=1, read at pf_create) share
+def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dtype):
+    """The one-launch cooperative step (pf_si_coop.cuh) and the per-kernel CG path (pf_set_option PF_OPT_SI_PER_KERNEL) share
     decomposition, arithmetic and summation trees: fields, iteration counts and residuals must agree bit for bit.
-    PF_SI_GRID_SYNC=1 replaces the flagged all-block sums of the cooperative step (GridSum, pf_si_coop.cuh) by grid.sync() +
+    PF_OPT_SI_GRID_SYNC replaces the flagged all-block sums of the cooperative step (GridSum, pf_si_coop.cuh) by grid.sync() +
     partial arrays - a third identical run."""
     kw = dict(neumann=dict(),
               periodic_aniso=dict(Phi_boundary="periodic", T_boundary="periodic", S=0.3),
@@ -428,8 +429,10 @@ def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dt
     npdt = np.float64 if dtype == PF_F64 else np.float32
     F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
 
-    def run():
+    def run(options=()):
         with S.Solver(nx, ny, dtype) as s:
+            for opt in options:
+                s.set_option(opt, 1)
             F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
             infos, launches0 = [], s.kernel_launches
             for _ in range(4):
@@ -438,14 +441,10 @@ def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dt
                 F, nF = nF, F; U, nU = nU, U
             return s.download(F), s.download(U), infos, s.kernel_launches - launches0
 
-    monkeypatch.delenv("PF_SI_PER_KERNEL", raising=False)
-    monkeypatch.delenv("PF_SI_GRID_SYNC", raising=False)
     cF, cU, cinfo, claunches = run()
-    monkeypatch.setenv("PF_SI_GRID_SYNC", "1")                          # cooperative grid.sync() + partial arrays instead of the flagged sums
-    gF_, gU_, ginfo, glaunches = run()
+    gF_, gU_, ginfo, glaunches = run([PF_OPT_SI_GRID_SYNC])             # cooperative grid.sync() + partial arrays instead of the flagged sums
     assert np.array_equal(cF, gF_) and np.array_equal(cU, gU_) and cinfo == ginfo and claunches == glaunches
-    monkeypatch.setenv("PF_SI_PER_KERNEL", "1")
-    kF, kU, kinfo, klaunches = run()
+    kF, kU, kinfo, klaunches = run([PF_OPT_SI_GRID_SYNC, PF_OPT_SI_PER_KERNEL])
     assert np.array_equal(cF, kF) and np.array_equal(cU, kU)
     assert cinfo == kinfo, (cinfo, kinfo)
     assert claunches < klaunches / 10, (claunches, klaunches)          # the cooperative path really ran
@@ -454,14 +453,19 @@ def test_semi_implicit_cooperative_step_equals_per_kernel_path(variant, size, dt
 
 @pytest.mark.parametrize("solver,dtype,host_dtype", [("explicit-rk4", PF_F64, PF_F64), ("explicit", PF_F64, PF_F64), ("explicit-rk4", PF_F32, PF_F32),
                                                      ("explicit-rk4", PF_F64, PF_F32), ("explicit-rk4-adaptive", PF_F64, PF_F64), ("semi-implicit", PF_F64, PF_F64)])
-def test_step_host_equals_upload_step_download(solver, dtype, host_dtype):
+@pytest.mark.parametrize("bc", ["neumann", "periodic"])
+def test_step_host_equals_upload_step_download(solver, dtype, host_dtype, bc):
     """pf_step_host (banded upload / compute / download pipeline for the fixed-step explicit solvers) returns exactly what the
-    three separate calls return, over several steps with the outputs fed back as inputs."""
+    three separate calls return, over several steps with the outputs fed back as inputs. The device fields are poisoned before
+    every call, so a band that computes before all of its inputs are uploaded (periodic: band 0 reads the wrapped last rows)
+    cannot pass on stale device contents."""
     nx, ny = 333, 700
-    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_tolerance=1e-7, T_tolerance=1e-7)
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_tolerance=1e-7, T_tolerance=1e-7, Phi_boundary=bc, T_boundary=bc)
     npdt = np.float64 if host_dtype == PF_F64 else np.float32
     F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    poison = np.full((ny, nx), np.nan, dtype=npdt)
     with S.Solver(nx, ny, dtype) as a, S.Solver(nx, ny, dtype) as b:
+        a.set_option(PF_OPT_HOST_BANDS, 10)
         aF, aU, anF, anU = a.field_alloc(), a.field_alloc(), a.field_alloc(), a.field_alloc()
         bF, bU, bnF, bnU = b.field_alloc(), b.field_alloc(), b.field_alloc(), b.field_alloc()
         hF, hU = F0.copy(), U0.copy()
@@ -471,6 +475,7 @@ def test_step_host_equals_upload_step_download(solver, dtype, host_dtype):
             L = S.lib()
             info = S.pf_step_info()
             import ctypes
+            a.upload(aF, poison); a.upload(aU, poison)
             a._ck(L.pf_step_host(a._h, ctypes.byref(p), hF.ctypes.data, hU.ctypes.data, oF.ctypes.data, oU.ctypes.data, host_dtype, aF, aU, anF, anU, ctypes.byref(info)))
             b.upload(bF, gF); b.upload(bU, gU)
             winfo = b.step(p, bF, bU, bnF, bnU)

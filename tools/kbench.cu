@@ -82,15 +82,14 @@ static void launch_tiled(const FusedArgs<Real>& a)
 template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
 static void launch_stream(FusedArgs<Real> a, int nch)
 {
-    const int chunk = (a.own_y1 - a.own_y0 + nch - 1) / nch;      // nch balanced chunks
     constexpr int NST = SchemeStages<SCHEME>::value, EWI = 32 * WARPS - 2 * NST;
     const size_t smem = stream_smem_bytes<Real, SCHEME, WARPS>();
     auto kern = k_stream_step<Real, SCHEME, ANISO, WARPS, MINB>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    a.chunk = chunk;
-    dim3 grid(stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC), (a.own_y1 - a.own_y0 + chunk - 1) / chunk), block(32 * WARPS);
-    kern<<<grid, block, smem>>>(a);
+    a.strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
+    a.nch = std::min(nch, a.own_y1 - a.own_y0);
+    kern<<<a.strips * a.nch, 32 * WARPS, smem>>>(a);
 }
 
 template <typename Real>
