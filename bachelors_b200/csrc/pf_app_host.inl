@@ -4,6 +4,61 @@
 
 extern "C" {
 
+// The reference's reduction micro-benchmark (run_benchmarks, simulation.cu:1300-1358) on this library's reductions.
+int pf_bench_reductions(pf_solver* s, size_t n, int value_dtype, int reps, double* seconds_max, double* seconds_stats, double* max_value)
+{
+    if(int rc = bind(s)) return rc;
+    if(n == 0 || reps < 1 || (value_dtype != PF_F32 && value_dtype != PF_F64)) return fail(s, PF_ERR_INVALID, "pf_bench_reductions: bad arguments");
+    const size_t es = pf_sizeof_real(value_dtype);
+    void *a = nullptr, *b = nullptr;
+    PF_CUDA(s, cudaMalloc(&a, n * es));
+    if(cudaMalloc(&b, n * es) != cudaSuccess) { cudaFree(a); cudaGetLastError(); return fail(s, PF_ERR_OOM, "pf_bench_reductions: out of memory"); }
+    const int fill_blocks = elementwise_blocks(s, n, 256);
+    const int red_blocks = (int) std::max<size_t>(1, std::min<size_t>((n / (16 / es) + 255) / 256, (size_t) s->sm_count * 8));
+    const int st_blocks = std::min<int>(CG_MAX_BLOCKS, elementwise_blocks(s, n, CG_THREADS));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    std::vector<float> t_max, t_stats;
+    int rc = PF_OK;
+    auto ck = [&](cudaError_t e) { if(e != cudaSuccess && rc == PF_OK) rc = fail(s, PF_ERR_CUDA, "pf_bench_reductions: %s", cudaGetErrorString(e)); };
+    ck(cudaEventCreate(&e0)); ck(cudaEventCreate(&e1));
+    if(value_dtype == PF_F64) { k_fill_hash<double><<<fill_blocks, 256, 0, s->stream>>>(n, (double*) a, 1u); k_fill_hash<double><<<fill_blocks, 256, 0, s->stream>>>(n, (double*) b, 2u); }
+    else                      { k_fill_hash<float><<<fill_blocks, 256, 0, s->stream>>>(n, (float*) a, 1u);  k_fill_hash<float><<<fill_blocks, 256, 0, s->stream>>>(n, (float*) b, 2u); }
+    s->launches += 2;
+    for(int r = -2; r < reps && rc == PF_OK; r++)                         // two warm-up rounds
+    {
+        float ms = 0;
+        ck(cudaEventRecord(e0, s->stream));
+        ck(cudaMemsetAsync(s->d_err, 0, sizeof(unsigned long long), s->stream));
+        if(value_dtype == PF_F64) k_reduce_maxabs<double><<<red_blocks, 256, 0, s->stream>>>(n, (const double*) a, s->d_err);
+        else                      k_reduce_maxabs<float><<<red_blocks, 256, 0, s->stream>>>(n, (const float*) a, s->d_err);
+        ck(cudaEventRecord(e1, s->stream)); ck(cudaEventSynchronize(e1)); ck(cudaEventElapsedTime(&ms, e0, e1));
+        if(r >= 0) t_max.push_back(ms);
+        ck(cudaEventRecord(e0, s->stream));
+        if(value_dtype == PF_F64) k_stats_delta<double><<<st_blocks, CG_THREADS, 0, s->stream>>>(n, (const double*) a, (const double*) b, s->d_stats);
+        else                      k_stats_delta<float><<<st_blocks, CG_THREADS, 0, s->stream>>>(n, (const float*) a, (const float*) b, s->d_stats);
+        ck(cudaEventRecord(e1, s->stream)); ck(cudaEventSynchronize(e1)); ck(cudaEventElapsedTime(&ms, e0, e1));
+        if(r >= 0) t_stats.push_back(ms);
+        s->launches += 2;
+    }
+    ck(cudaGetLastError());
+    if(rc == PF_OK)
+    {
+        ck(cudaMemcpyAsync(s->h_err, s->d_err, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+        ck(cudaStreamSynchronize(s->stream));
+    }
+    if(rc == PF_OK)
+    {
+        std::sort(t_max.begin(), t_max.end()); std::sort(t_stats.begin(), t_stats.end());
+        if(seconds_max) *seconds_max = t_max[t_max.size() / 2] * 1e-3;
+        if(seconds_stats) *seconds_stats = t_stats[t_stats.size() / 2] * 1e-3;
+        if(max_value) *max_value = value_dtype == PF_F64 ? decode_err<double>(s->h_err[0]) : (double) decode_err<float>(s->h_err[0]);
+    }
+    if(e0) cudaEventDestroy(e0);
+    if(e1) cudaEventDestroy(e1);
+    cudaFree(a); cudaFree(b);
+    return rc;
+}
+
 int pf_init_fields(pf_solver* s, const pf_params* params, const pf_initial* init, void* F, void* U)
 {
     if(int rc = bind(s)) return rc;

@@ -4,6 +4,7 @@
 // The explicit solvers normally run through pf_fused.cuh; the kernels here serve pf_rhs(), mixed
 // Phi/T boundary types, the Euler corrector loop, and the whole semi-implicit solver.
 #pragma once
+#include <type_traits>
 #include "pf_common.cuh"
 
 namespace pf {
@@ -478,15 +479,29 @@ k_stats_delta(size_t N, const Real* __restrict__ a, const Real* __restrict__ b, 
 {
     __shared__ Real scratch[32];
     Real sum = 0, L1 = 0, L2 = 0, mn = (Real) INFINITY, mx = -(Real) INFINITY;
-    for(size_t i = blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < N; i += (size_t) gridDim.x * CG_THREADS)
+    auto take = [&](const Real v)
     {
-        const Real v = a[i] - b[i];
         sum += v;
         L1 += v >= 0 ? v : -v;
         L2 = pf_fma(v, v, L2);
         mn = v < mn ? v : mn;
         mx = v > mx ? v : mx;
+    };
+    // 16-byte loads (fields come from cudaMalloc: aligned); a thread's values are taken in index order, so the result does not
+    // depend on the load width
+    constexpr int V = 16 / sizeof(Real);
+    using Vec = typename std::conditional<sizeof(Real) == 8, double2, float4>::type;
+    const bool vec_ok = ((reinterpret_cast<size_t>(a) | reinterpret_cast<size_t>(b)) & 15) == 0;
+    const size_t nv = vec_ok ? N / V : 0, stride = (size_t) gridDim.x * CG_THREADS;
+    for(size_t i = blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < nv; i += stride)
+    {
+        const Vec va = reinterpret_cast<const Vec*>(a)[i], vb = reinterpret_cast<const Vec*>(b)[i];
+        const Real* ea = reinterpret_cast<const Real*>(&va); const Real* eb = reinterpret_cast<const Real*>(&vb);
+        #pragma unroll
+        for(int k = 0; k < V; k++) take(ea[k] - eb[k]);
     }
+    for(size_t i = nv * V + blockIdx.x * (size_t) CG_THREADS + threadIdx.x; i < N; i += stride)
+        take(a[i] - b[i]);
     sum = block_sum(sum, scratch);
     L1 = block_sum(L1, scratch);
     L2 = block_sum(L2, scratch);
@@ -500,6 +515,67 @@ k_stats_delta(size_t N, const Real* __restrict__ a, const Real* __restrict__ b, 
         for(int w = 1; w < CG_THREADS / 32; w++) { mn = smn[w] < mn ? smn[w] : mn; mx = smx[w] > mx ? smx[w] : mx; }
         StatsPartial o; o.sum = (double) sum; o.L1 = (double) L1; o.L2 = (double) L2; o.mn = (double) mn; o.mx = (double) mx;
         partials[blockIdx.x] = o;
+    }
+}
+
+// ---- the reduction micro-benchmark's kernels (pf_bench_reductions; reference run_benchmarks, simulation.cu:1300-1358) --------
+// max |x| over N values: 16-byte loads, warp shuffle tree, ONE integer atomicMax per warp on the IEEE bit pattern - the reduction
+// the Merson error norm uses (atomic_max_nonneg), which replaces the reference's multi-pass cuda_reduce(Reduce::MAX).
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_reduce_maxabs(size_t N, const T* __restrict__ x, unsigned long long* bits)
+{
+    constexpr int V = 16 / sizeof(T), UNR = 4;
+    using Vec = typename std::conditional<sizeof(T) == 8, double2, float4>::type;
+    T m = 0;
+    const size_t nv = N / V, stride = (size_t) gridDim.x * blockDim.x;
+    const Vec* xv = reinterpret_cast<const Vec*>(x);
+    size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x;
+    for(; i + (UNR - 1) * stride < nv; i += UNR * stride)                 // UNR independent 16-byte loads in flight per thread
+    {
+        Vec v[UNR];
+        #pragma unroll
+        for(int u = 0; u < UNR; u++) v[u] = xv[i + u * stride];
+        #pragma unroll
+        for(int u = 0; u < UNR; u++)
+        {
+            const T* e = reinterpret_cast<const T*>(&v[u]);
+            #pragma unroll
+            for(int k = 0; k < V; k++) { const T a = e[k] >= 0 ? e[k] : -e[k]; m = a > m ? a : m; }
+        }
+    }
+    for(; i < nv; i += stride)
+    {
+        const Vec v = xv[i];
+        const T* e = reinterpret_cast<const T*>(&v);
+        #pragma unroll
+        for(int k = 0; k < V; k++) { const T a = e[k] >= 0 ? e[k] : -e[k]; m = a > m ? a : m; }
+    }
+    for(size_t j = nv * V + blockIdx.x * (size_t) blockDim.x + threadIdx.x; j < N; j += stride)
+    {
+        const T a = x[j] >= 0 ? x[j] : -x[j]; m = a > m ? a : m;
+    }
+    __shared__ T sm[8];
+    m = warp_max(m);
+    if((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if(threadIdx.x == 0)
+    {
+        #pragma unroll
+        for(int w = 1; w < 8; w++) m = sm[w] > m ? sm[w] : m;
+        if(m > 0) atomic_max_nonneg(bits, m);                              // one atomic per block
+    }
+}
+
+// uniform values in [0, 1) from an integer hash of the index (the benchmark's random_map_32, simulation.cu:1316)
+template <typename T>
+__global__ void k_fill_hash(size_t N, T* x, unsigned seed)
+{
+    for(size_t i = blockIdx.x * (size_t) blockDim.x + threadIdx.x; i < N; i += (size_t) gridDim.x * blockDim.x)
+    {
+        unsigned h = (unsigned) i * 2654435761u ^ seed;
+        h ^= h >> 16; h *= 0x7feb352du; h ^= h >> 15; h *= 0x846ca68bu; h ^= h >> 16;
+        x[i] = (T)((h >> 8) * (1.0f / 16777216.0f));
     }
 }
 

@@ -10,6 +10,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <string>
+#include <vector>
 #include <algorithm>
 
 #include "../../include/pf_solver.h"
@@ -52,6 +53,12 @@ struct pf_solver {
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
+    int stream_resident[16];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
+    unsigned* run_progress = nullptr;       // multi-step launches: steps finished by each unit (+ 1 flag word), see StreamRun
+    int run_progress_units = 0;
+    unsigned run_base = 0;                  // progress value meaning "nothing of the next launch done yet"
+    int run_steps = 1;                      // steps the next fused launch advances (set by pf_run around its launch)
+    bool run_used = false;                  // the last fused launch really was a multi-step launch
     int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
     unsigned long long* ll_slots = nullptr; // flagged partial sums of the cooperative semi-implicit step (pf_si_coop.cuh GridSum)
     unsigned ll_epoch = 1;                  // next unused epoch (0 = the cleared slots)
@@ -172,6 +179,7 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     if(device < 0 || device >= ndev) return fail(nullptr, PF_ERR_INVALID, "pf_create: device %d out of range (%d devices)", device, ndev);
 
     pf_solver* s = new pf_solver();
+    memset(s->stream_resident, 0, sizeof s->stream_resident);
     s->device = device; s->dtype = dtype; s->nx = nx; s->ny = ny_global; s->slab = *slab;
     s->ghost_lo = slab->has_lo ? slab->ghost : 0;
     s->ghost_hi = slab->has_hi ? slab->ghost : 0;
@@ -211,6 +219,7 @@ void pf_destroy(pf_solver* s)
     for(int i = 0; i < PF_SCRATCH_SLOTS; i++) if(s->scratch[i]) cudaFree(s->scratch[i]);
     if(s->partials) cudaFree(s->partials);
     if(s->ll_slots) cudaFree(s->ll_slots);
+    if(s->run_progress) cudaFree(s->run_progress);
     if(s->d_cg) cudaFree(s->d_cg);
     if(s->d_stats) cudaFree(s->d_stats);
     if(s->d_err) cudaFree(s->d_err);
@@ -474,19 +483,62 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
     auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
+    auto kern_run = k_stream_run<Real, SCHEME, ANISO, W, MINB>;
     const size_t smem = stream_smem_bytes<Real, SCHEME, W>();
     if(!(s->stream_attr_done & (1u << inst_bit)))
     {
         PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         s->stream_attr_done |= 1u << inst_bit;
     }
     const int own_rows = a.own_y1 - a.own_y0;
+    s->run_used = false;
     if(own_rows <= 0) return PF_OK;
     a.strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
     a.nch = stream_chunks(s->sm_count, MINB, a.strips, own_rows, StreamGeom<SCHEME>::FILL);
     const long long units = (long long) a.strips * a.nch;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
+    if(s->run_steps > 1 && SCHEME != SCHEME_RKM)
+    {
+        // Multi-step launch (pf_run): every unit must be resident at once and a tile may only depend on its 8 neighbours.
+        if(!s->stream_resident[inst_bit])
+        {
+            int coop = 0, per_sm = 0;
+            PF_CUDA(s, cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, s->device));
+            if(coop) PF_CUDA(s, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern_run, 32 * W, smem));
+            s->stream_resident[inst_bit] = coop && per_sm > 0 ? per_sm : -1;
+        }
+        const bool whole_grid = s->is_full_grid() && s->win_y1 <= s->win_y0;
+        // one wave, and chunks of at least 2 x NST rows (a tile then only depends on its 8 neighbours): fewer chunks if need be
+        const long long slots = s->stream_resident[inst_bit] > 0 ? (long long) s->stream_resident[inst_bit] * s->sm_count : 0;
+        const int nch_run = (int) std::min<long long>({(long long) a.nch, (long long)(own_rows / (2 * NST)), slots / a.strips});
+        if(whole_grid && nch_run >= 1)
+        {
+            a.nch = nch_run;
+            const long long units = (long long) a.strips * a.nch;
+            if(s->run_progress_units < units)
+            {
+                if(s->run_progress) { PF_CUDA(s, cudaStreamSynchronize(s->stream)); PF_CUDA(s, cudaFree(s->run_progress)); s->run_progress = nullptr; }
+                PF_CUDA(s, cudaMalloc((void**) &s->run_progress, (size_t)(units + 1) * sizeof(unsigned)));
+                s->run_progress_units = (int) units;
+                s->run_base = 0;
+            }
+            if(s->run_base == 0 || s->run_base > 0x7f000000u)             // first use / before the counter can wrap: start over from zeroed words
+            {
+                PF_CUDA(s, cudaMemsetAsync(s->run_progress, 0, (size_t)(s->run_progress_units + 1) * sizeof(unsigned), stream));
+                s->run_base = 1;
+            }
+            StreamRun r; r.n_steps = s->run_steps; r.base = s->run_base; r.progress = s->run_progress; r.units = s->run_progress_units;
+            s->run_base += (unsigned) s->run_steps;
+            void* args[] = {&a, &r};
+            PF_CUDA(s, cudaLaunchCooperativeKernel((const void*) kern_run, dim3((unsigned) units), dim3(32 * W), args, smem, stream));
+            PF_LAUNCH_CHECK(s);
+            s->run_used = true;
+            return PF_OK;
+        }
+    }
     kern<<<(unsigned) units, 32 * W, smem, stream>>>(a);
     PF_LAUNCH_CHECK(s);
     return PF_OK;
@@ -1060,20 +1112,57 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
     int64_t i = 0;
     // fixed-dt solvers without statistics never need the host between steps: enqueue everything, synchronise once
     const bool async_ok = p.solver != PF_SOLVER_EXPLICIT_RK4_ADAPTIVE && !p.do_stats && !p.do_stats_step_residual;
-    for(; i < n_steps; i++)
+    // the fixed-step explicit solvers on the single-kernel path: ONE launch per batch of steps (k_stream_step, StreamRun)
+    const bool multi_ok = async_ok && (p.solver == PF_SOLVER_EXPLICIT_EULER || p.solver == PF_SOLVER_EXPLICIT_RK4) && !p.do_corrector_loop &&
+                          !p.do_corrector_guess && fused_eligible(s, p) && (s->last_num_steps % 2) == 0 && s->is_full_grid();
+    while(i < n_steps)
     {
         if(stop_time > 0 && stop_time - t < 1e-16) break;                  // main.cpp:525
         p.iter = params->iter + i; p.time = t;
-        const bool last = (i + 1 == n_steps) || (stop_time > 0 && stop_time - (t + p.dt) < 1e-16 && async_ok);
+        int64_t batch = 1;
+        if(multi_ok)
+        {
+            // how many steps until the stop time (the same additions of dt the loop below would make), at most 2^20 per launch
+            double tt = t;
+            batch = 0;
+            while(i + batch < n_steps && batch < (1 << 20) && !(stop_time > 0 && stop_time - tt < 1e-16)) { tt += p.dt; batch++; }
+        }
         pf_step_info info;
-        int rc = s->dtype == PF_F64 ? step_impl<double>(s, p, cF, cU, nF, nU, &info, !async_ok || last)
-                                    : step_impl<float>(s, p, cF, cU, nF, nU, &info, !async_ok || last);
-        if(rc) return rc;
+        if(batch > 1)
+        {
+            s->run_steps = (int) batch;
+            int rc = s->dtype == PF_F64 ? step_impl<double>(s, p, cF, cU, nF, nU, &info, false) : step_impl<float>(s, p, cF, cU, nF, nU, &info, false);
+            s->run_steps = 1;
+            if(rc) return rc;
+            if(s->run_used)
+            {
+                for(int64_t k = 0; k < batch; k++) t += info.dt_advanced;    // the same floating-point additions as step by step
+                i += batch;
+                if(batch & 1) { std::swap(cF, nF); std::swap(cU, nU); }
+                if(last_info) *last_info = info;
+                continue;
+            }
+            // the grid does not fit one wave (or the device cannot launch cooperatively): that was a plain single step
+        }
+        else
+        {
+            const bool last = (i + 1 == n_steps) || (stop_time > 0 && stop_time - (t + p.dt) < 1e-16 && async_ok);
+            int rc = s->dtype == PF_F64 ? step_impl<double>(s, p, cF, cU, nF, nU, &info, !async_ok || last)
+                                        : step_impl<float>(s, p, cF, cU, nF, nU, &info, !async_ok || last);
+            if(rc) return rc;
+        }
         t += info.dt_advanced;
         if(last_info) *last_info = info;
         std::swap(cF, nF); std::swap(cU, nU);
+        i++;
     }
     PF_CUDA(s, cudaStreamSynchronize(s->stream));
+    if(s->run_progress)
+    {
+        unsigned stalled = 0;
+        PF_CUDA(s, cudaMemcpy(&stalled, s->run_progress + s->run_progress_units, sizeof stalled, cudaMemcpyDeviceToHost));
+        if(stalled) { cudaMemset(s->run_progress + s->run_progress_units, 0, sizeof stalled); return fail(s, PF_ERR_CUDA, "pf_run: a multi-step launch stalled (its CTAs were not co-resident)"); }
+    }
     if(F_out) *F_out = cF;
     if(U_out) *U_out = cU;
     if(steps_done) *steps_done = i;

@@ -80,6 +80,8 @@ struct StreamState {
 template <typename Real>
 struct StreamCtx {
     using V2 = typename Vec2T<Real>::type;
+    const Real* F; const Real* U;      // y(n) of the step being computed (a multi-step launch swaps the roles of the buffers every step)
+    Real* out_F; Real* out_U;          // y(n+1)
     V2* ybuf;                          // ring of canon y rows, offset to this thread's slot
     V2* cbuf;                          // U-deep ring of the stage-input rows of stages 2..NST, offset to this thread's slot
     unsigned lx;                       // clamped / wrapped column for loads
@@ -230,8 +232,8 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
         if(c.st_ok)
         {
             const unsigned idx = (unsigned)(row - a.row0) * (unsigned) a.nx + c.gxu;
-            a.out_F[idx] = nF;
-            a.out_U[idx] = nT;
+            c.out_F[idx] = nF;
+            c.out_U[idx] = nT;
         }
     }
 }
@@ -258,7 +260,7 @@ __device__ __forceinline__ unsigned stream_mem_row(const FusedArgs<Real>& a, int
 }
 
 // One row of the march. PH = it mod U.
-template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool CHECKED, int PH>
+template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
 __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                  const int it, const int rlo, const int rhi)
 {
@@ -269,13 +271,14 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
     const int g1 = c.G0 + it;
     // 1. prefetch the raw y of row g1 + 2, retired at the end of this iteration
     const unsigned ro = (CHECKED ? stream_mem_row(a, g1 + 1 + 1, rlo, rhi) : (unsigned)(g1 + 1 + 1 - a.row0)) * (unsigned) a.nx + c.lx;
-    const Real tF = a.F[ro], tT = a.U[ro];
+    // COHERENT (multi-step launches): L2 only - another SM rewrites these rows every other step, and L1 is not coherent across SMs
+    const Real tF = COHERENT ? __ldcg(c.F + ro) : c.F[ro], tT = COHERENT ? __ldcg(c.U + ro) : c.U[ro];
     if(!CHECKED && g1 + 2 + G::L2_AHEAD <= rhi)
     {
         // pull the rows this CTA reads a few iterations from now into L2 (measured: -1.5 % on the RK4 step at 2048^2)
         const unsigned po = ro + (unsigned) G::L2_AHEAD * (unsigned) a.nx;
-        asm volatile("prefetch.global.L2 [%0];" :: "l"(a.F + po));
-        asm volatile("prefetch.global.L2 [%0];" :: "l"(a.U + po));
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(c.F + po));
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(c.U + po));
     }
     // 2. publish y of row g1 + 1: the E/W neighbours of stage 1 in the NEXT iteration, and the y the later stages re-read
     V2* const ypub = c.ybuf + ((g1 + 1) & (G::YR - 1)) * ROWSTRIDE;
@@ -304,14 +307,14 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
     __syncthreads();
 }
 
-template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool CHECKED, int PH>
+template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
 struct StreamIters {
     static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                const int it0, const int rlo, const int rhi)
     {
-        stream_iteration<Real, SCHEME, ANISO, EW, EDGE, CHECKED, PH>(a, c, st, it0 + PH, rlo, rhi);
+        stream_iteration<Real, SCHEME, ANISO, EW, EDGE, COHERENT, CHECKED, PH>(a, c, st, it0 + PH, rlo, rhi);
         if constexpr (PH + 1 < StreamGeom<SCHEME>::U)
-            StreamIters<Real, SCHEME, ANISO, EW, EDGE, CHECKED, PH + 1>::run(a, c, st, it0, rlo, rhi);
+            StreamIters<Real, SCHEME, ANISO, EW, EDGE, COHERENT, CHECKED, PH + 1>::run(a, c, st, it0, rlo, rhi);
     }
 };
 
@@ -331,32 +334,43 @@ constexpr size_t stream_smem_bytes()
 }
 
 // Work decomposition: a CTA = one unit (1-D grid) = a strip of EW columns x a chunk of rows; the chunks of a strip are
-// balanced (lengths differ by at most one row).
-template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
-__global__ void __launch_bounds__(32 * WARPS, MINB)
-k_stream_step(const FusedArgs<Real> a)
+// balanced (lengths differ by at most one row). Units in dispatch order: the two edge strips of a non-periodic grid first
+// (their CTAs do a little more per row, and the CTAs dispatched first get the SM's oldest, i.e. fastest, resident slot), then
+// the interior strips.
+template <typename Real>
+__device__ __forceinline__ void stream_unit_to_tile(const FusedArgs<Real>& a, const bool periodic, const int unit, int& strip, int& chunk)
+{
+    if(periodic || a.strips < 3) { strip = unit % a.strips; chunk = unit / a.strips; }
+    else if(unit < 2 * a.nch)    { strip = (unit & 1) ? a.strips - 1 : 0; chunk = unit >> 1; }
+    else                         { const int v = unit - 2 * a.nch; strip = 1 + v % (a.strips - 2); chunk = v / (a.strips - 2); }
+}
+template <typename Real>
+__device__ __forceinline__ int stream_tile_to_unit(const FusedArgs<Real>& a, const bool periodic, const int strip, const int chunk)
+{
+    if(periodic || a.strips < 3) return strip + a.strips * chunk;
+    if(strip == 0) return 2 * chunk;
+    if(strip == a.strips - 1) return 2 * chunk + 1;
+    return 2 * a.nch + (strip - 1) + (a.strips - 2) * chunk;
+}
+
+// One time step of one unit: y(n) = (F, U) -> y(n+1) = (out_F, out_U).
+template <typename Real, int SCHEME, bool ANISO, int WARPS, bool COHERENT>
+__device__ __forceinline__ void stream_unit(const FusedArgs<Real>& a, const Real* in_F, const Real* in_U, Real* out_F, Real* out_U,
+                                            typename Vec2T<Real>::type* const smem, const int strip, const int chunk)
 {
     using V2 = typename Vec2T<Real>::type;
     using G = StreamGeom<SCHEME>;
     constexpr int NST = G::NST, U = G::U;
     constexpr int H = NST, EW = 32 * WARPS, EWI = EW - 2 * H, ROWSTRIDE = EW + 2;
     constexpr int RING_ELEMS = (G::YR + U * (NST - 1)) * ROWSTRIDE;
-    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
-    V2* const smem = reinterpret_cast<V2*>(pf_smem_raw);
     const int cx = (int) threadIdx.x;
 
     const int nx = a.nx, NY = a.ny_global;
     const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
     const int own_rows = a.own_y1 - a.own_y0;
-    // units in dispatch order: the two edge strips of a non-periodic grid first (their CTAs do a little more per row, and
-    // the CTAs dispatched first get the SM's oldest, i.e. fastest, resident slot), then the interior strips
-    const int unit = (int) blockIdx.x;
-    int strip, chunk;
-    if(periodic || a.strips < 3) { strip = unit % a.strips; chunk = unit / a.strips; }
-    else if(unit < 2 * a.nch)    { strip = (unit & 1) ? a.strips - 1 : 0; chunk = unit >> 1; }
-    else                         { const int v = unit - 2 * a.nch; strip = 1 + v % (a.strips - 2); chunk = v / (a.strips - 2); }
 
     StreamCtx<Real> c;
+    c.F = in_F; c.U = in_U; c.out_F = out_F; c.out_U = out_U;
     // Periodic: strip k owns columns [k*EWI, (k+1)*EWI), its threads start H columns to the left (wrapped).
     // Non-periodic: nothing outside the domain is needed (the edge thread publishes the ghost pair itself), so thread 0 of
     // strip 0 IS column 0, and every column of the first / last strip up to the domain edge is clean:
@@ -408,7 +422,7 @@ k_stream_step(const FusedArgs<Real> a)
     for(int d = -1; d <= 1; d++)
     {
         const unsigned ro = stream_mem_row(a, c.G0 + d, rlo, rhi) * (unsigned) nx + c.lx;
-        const Real f = a.F[ro], u = a.U[ro];
+        const Real f = COHERENT ? __ldcg(c.F + ro) : c.F[ro], u = COHERENT ? __ldcg(c.U + ro) : c.U[ro];
         const int j = d < 0 ? U - 1 : d;
         st.yF[j] = canon_zero(f); st.yT[j] = canon_zero(u);
         st.negmask = (st.negmask << 2) | (unsigned) is_negzero(f) | ((unsigned) is_negzero(u) << 1);
@@ -430,14 +444,14 @@ k_stream_step(const FusedArgs<Real> a)
     if(edge_strip)
         for(int it0 = 0; it0 < n_it; it0 += U)
         {
-            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, true, false, 0>::run(a, c, st, it0, rlo, rhi);
-            else                                 StreamIters<Real, SCHEME, ANISO, EW, true, true, 0>::run(a, c, st, it0, rlo, rhi);
+            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, true, COHERENT, false, 0>::run(a, c, st, it0, rlo, rhi);
+            else                                 StreamIters<Real, SCHEME, ANISO, EW, true, COHERENT, true, 0>::run(a, c, st, it0, rlo, rhi);
         }
     else
         for(int it0 = 0; it0 < n_it; it0 += U)
         {
-            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, false, false, 0>::run(a, c, st, it0, rlo, rhi);
-            else                                 StreamIters<Real, SCHEME, ANISO, EW, false, true, 0>::run(a, c, st, it0, rlo, rhi);
+            if(it0 >= lo_it && it0 + U <= hi_it) StreamIters<Real, SCHEME, ANISO, EW, false, COHERENT, false, 0>::run(a, c, st, it0, rlo, rhi);
+            else                                 StreamIters<Real, SCHEME, ANISO, EW, false, COHERENT, true, 0>::run(a, c, st, it0, rlo, rhi);
         }
 
     if(SCHEME == SCHEME_RKM)
@@ -448,6 +462,89 @@ k_stream_step(const FusedArgs<Real> a)
             if(eF > 0) atomic_max_nonneg(a.err_bits + 0, eF);
             if(eT > 0) atomic_max_nonneg(a.err_bits + 1, eT);
         }
+    }
+}
+
+// ---- multi-step launches -----------------------------------------------------------------------------------------------
+// n_steps > 1: ONE launch advances n_steps fixed-size time steps. All units are co-resident (cooperative launch: one wave) and
+// keep their tile; the buffers swap roles every step. There is no grid-wide barrier: a unit may start step m as soon as its
+// 8 neighbouring tiles (and itself) have finished step m - 1 - their rows / columns are the only ones it reads (halo H <= the
+// tile extents) and, the ping-pong being what it is, the only readers of what it is about to overwrite. progress[u] counts the
+// steps unit u has finished (base + k; base grows from launch to launch, so the words are never reset).
+// Writer: all stores, __syncthreads, thread 0: fence + st.release. Reader: ld.acquire by the polling threads, __syncthreads,
+// then ld.global.cg (the fields are never read through L1, which is not coherent across SMs).
+struct StreamRun {
+    int n_steps;
+    unsigned base;
+    unsigned* progress;                // [units] + 1 word: set to 1 by a unit that gave up waiting (co-residency violated)
+    int units;
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p)
+{
+    unsigned v; asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
+// One time step per launch.
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB)
+k_stream_step(const FusedArgs<Real> a)
+{
+    using V2 = typename Vec2T<Real>::type;
+    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
+    int strip, chunk;
+    stream_unit_to_tile(a, a.bc == PF_BOUNDARY_PERIODIC, (int) blockIdx.x, strip, chunk);
+    stream_unit<Real, SCHEME, ANISO, WARPS, false>(a, a.F, a.U, a.out_F, a.out_U, reinterpret_cast<V2*>(pf_smem_raw), strip, chunk);
+}
+
+// r.n_steps time steps per launch (cooperative launch: all units co-resident).
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB)
+k_stream_run(const FusedArgs<Real> a, const StreamRun r)
+{
+    using V2 = typename Vec2T<Real>::type;
+    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
+    V2* const smem = reinterpret_cast<V2*>(pf_smem_raw);
+    const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
+    const int unit = (int) blockIdx.x;
+    int strip, chunk;
+    stream_unit_to_tile(a, periodic, unit, strip, chunk);
+    // the tile this thread polls (threads 0..7: the 8 neighbours; -1: none, e.g. beyond a non-periodic edge)
+    int watch = -1;
+    if(threadIdx.x < 8)
+    {
+        const int k = (int) threadIdx.x + (threadIdx.x >= 4 ? 1 : 0);      // 0..8 without the centre
+        int s2 = strip + k % 3 - 1, c2 = chunk + k / 3 - 1;
+        if(periodic) s2 = (s2 + a.strips) % a.strips;
+        if(a.wrap_y) c2 = (c2 + a.nch) % a.nch;
+        if(s2 >= 0 && s2 < a.strips && c2 >= 0 && c2 < a.nch) watch = stream_tile_to_unit(a, periodic, s2, c2);
+        if(watch == unit) watch = -1;
+    }
+    for(int step = 0; step < r.n_steps; step++)
+    {
+        if(step > 0)
+        {
+            if(watch >= 0)
+            {
+                const unsigned want = r.base + (unsigned) step;
+                unsigned spins = 0;
+                while((int)(ld_acquire_u32(r.progress + watch) - want) < 0)
+                {
+                    __nanosleep(40);
+                    if(++spins > (1u << 24)) { r.progress[r.units] = 1; break; }      // ~ a second: the grid is not co-resident; the host reports it
+                }
+            }
+            __syncthreads();
+        }
+        const bool odd = step & 1;
+        stream_unit<Real, SCHEME, ANISO, WARPS, true>(a, odd ? a.out_F : a.F, odd ? a.out_U : a.U,
+                                                 odd ? const_cast<Real*>(a.F) : a.out_F, odd ? const_cast<Real*>(a.U) : a.out_U, smem, strip, chunk);
+        __syncthreads();
+        if(threadIdx.x == 0) { __threadfence(); st_release_u32(r.progress + unit, r.base + (unsigned) step + 1u); }
     }
 }
 

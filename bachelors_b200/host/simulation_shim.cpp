@@ -34,6 +34,47 @@ void shim_check(pf_solver* s, int rc, const char* what)
     abort();
 }
 
+// Which handle allocated a device pointer: sim_realloc frees and sim_modify* copies through the OWNING handle (its stream, its
+// staging buffer, its device), whatever other grid sizes are live.
+struct Shim_Alloc { void* ptr; pf_solver* s; };
+enum { SHIM_MAX_ALLOCS = 256 };
+Shim_Alloc g_allocs[SHIM_MAX_ALLOCS];
+int g_alloc_count = 0;
+
+void remember_alloc(void* ptr, pf_solver* s)
+{
+    if(g_alloc_count == SHIM_MAX_ALLOCS) { fprintf(stderr, "FATAL [pf_solver] more than %d live maps\n", (int) SHIM_MAX_ALLOCS); abort(); }
+    g_allocs[g_alloc_count++] = Shim_Alloc{ptr, s};
+}
+
+// Owner of the allocation that CONTAINS ptr (sim_modify may be handed an interior pointer); field sizes come from the handle.
+pf_solver* owner_of(const void* ptr, bool forget)
+{
+    for(int i = 0; i < g_alloc_count; i++)
+    {
+        int rows = 0;
+        pf_field_rows(g_allocs[i].s, &rows, NULL);
+        const char* base = (const char*) g_allocs[i].ptr;
+        size_t bytes = 0;
+        for(int k = 0; k < g_solver_count; k++)
+            if(g_solvers[k].s == g_allocs[i].s) bytes = (size_t) g_solvers[k].nx * (size_t) rows * sizeof(Real);
+        if((const char*) ptr >= base && (const char*) ptr < base + (bytes ? bytes : 1))
+        {
+            pf_solver* s = g_allocs[i].s;
+            if(forget) g_allocs[i] = g_allocs[--g_alloc_count];
+            return s;
+        }
+    }
+    fprintf(stderr, "FATAL [pf_solver] %p is not device memory of a live Sim_Map\n", ptr);
+    abort();
+}
+
+bool solver_has_allocs(pf_solver* s)
+{
+    for(int i = 0; i < g_alloc_count; i++) if(g_allocs[i].s == s) return true;
+    return false;
+}
+
 // One solver handle per grid size; the reference's maps of one run all share a size (main.cpp:164-168).
 pf_solver* solver_for(int nx, int ny)
 {
@@ -42,9 +83,12 @@ pf_solver* solver_for(int nx, int ny)
             return g_solvers[i].s;
     if(g_solver_count == SHIM_MAX_SOLVERS)
     {
-        // recycle the oldest handle (its fields were freed by sim_realloc(..., 0, 0) between runs, main.cpp:568-571)
-        pf_destroy(g_solvers[0].s);
-        memmove(g_solvers, g_solvers + 1, sizeof(Shim_Solver) * (SHIM_MAX_SOLVERS - 1));
+        // recycle the oldest handle without live maps (sim_realloc(..., 0, 0) frees them between runs, main.cpp:568-571)
+        int victim = -1;
+        for(int i = 0; i < g_solver_count && victim < 0; i++) if(!solver_has_allocs(g_solvers[i].s)) victim = i;
+        if(victim < 0) { fprintf(stderr, "FATAL [pf_solver] %d grid sizes with live maps\n", (int) SHIM_MAX_SOLVERS); abort(); }
+        pf_destroy(g_solvers[victim].s);
+        memmove(g_solvers + victim, g_solvers + victim + 1, sizeof(Shim_Solver) * (size_t)(g_solver_count - victim - 1));
         g_solver_count--;
     }
     int device = 0;
@@ -53,11 +97,6 @@ pf_solver* solver_for(int nx, int ny)
     shim_check(NULL, pf_create(&s, device, SHIM_DTYPE, nx, ny), "pf_create");
     g_solvers[g_solver_count++] = Shim_Solver{s, nx, ny};
     return s;
-}
-
-pf_solver* any_solver()
-{
-    return g_solver_count > 0 ? g_solvers[g_solver_count - 1].s : solver_for(1, 1);
 }
 
 pf_params to_pf_params(const Sim_Params& q)
@@ -104,7 +143,8 @@ void sim_realloc(Sim_Map* map, const char* name, int nx, int ny, double time, i6
     {
         if(map->data)
         {
-            shim_check(any_solver(), pf_field_free(any_solver(), map->data), "pf_field_free");
+            pf_solver* owner = owner_of(map->data, true);
+            shim_check(owner, pf_field_free(owner, map->data), "pf_field_free");
             map->data = NULL;
         }
         if((size_t) nx * (size_t) ny > 0)
@@ -112,6 +152,7 @@ void sim_realloc(Sim_Map* map, const char* name, int nx, int ny, double time, i6
             pf_solver* s = solver_for(nx, ny);
             void* dev = NULL;
             shim_check(s, pf_field_alloc(s, &dev), "pf_field_alloc");
+            remember_alloc(dev, s);
             map->data = (Real*) dev;
         }
         map->nx = nx;
@@ -193,36 +234,63 @@ double sim_step(Sim_Map F, Sim_Map U, Sim_Map* next_F, Sim_Map* next_U, Sim_Para
 // reference simulation.cu:1051-1067
 extern "C" void sim_modify(void* device_memory, void* host_memory, size_t size, Sim_Modify modify)
 {
-    pf_solver* s = any_solver();
+    pf_solver* s = owner_of(device_memory, false);
     if(modify == MODIFY_UPLOAD) shim_check(s, pf_upload_raw(s, device_memory, host_memory, size), "pf_upload_raw");
     else                        shim_check(s, pf_download_raw(s, device_memory, host_memory, size), "pf_download_raw");
 }
 
 extern "C" void sim_modify_float(Real* device_memory, float* host_memory, size_t count, Sim_Modify modify)
 {
-    pf_solver* s = any_solver();
+    pf_solver* s = owner_of(device_memory, false);
     if(modify == MODIFY_UPLOAD) shim_check(s, pf_upload(s, device_memory, host_memory, count, PF_F32), "pf_upload");
     else                        shim_check(s, pf_download(s, device_memory, host_memory, count, PF_F32), "pf_download");
 }
 
 extern "C" void sim_modify_double(Real* device_memory, double* host_memory, size_t count, Sim_Modify modify)
 {
-    pf_solver* s = any_solver();
+    pf_solver* s = owner_of(device_memory, false);
     if(modify == MODIFY_UPLOAD) shim_check(s, pf_upload(s, device_memory, host_memory, count, PF_F64), "pf_upload");
     else                        shim_check(s, pf_download(s, device_memory, host_memory, count, PF_F64), "pf_download");
 }
 
-// The reference compiles its GPU self-tests into the binary (simulation.cu:1368-1380); this repository's tests live in
-// tests/ (pytest, CPU oracle + golden vectors of the reference). The entry points stay so that main.cpp links.
+// The reference compiles self-tests of its generic launch / reduction helpers into the binary (simulation.cu:1368-1380); those
+// helpers do not exist here (this repository's tests are tests/, pytest against the CPU oracle and the reference's golden
+// vectors). What can be checked from inside the host process is checked: the library answers, a step runs, and the two
+// reductions reduce a known sequence to the known answers.
 extern "C" bool run_tests()
 {
-    fprintf(stderr, "run_tests: the B200 solver is tested by `python -m pytest tests -m gpu` in its own repository\n");
-    return true;
+    bool ok = pf_abi_version() == PF_ABI_VERSION && pf_device_count() > 0;
+    if(ok)
+    {
+        pf_solver* s = solver_for(64, 64);
+        double t_max = 0, t_stats = 0, mx = -1;
+        ok = pf_bench_reductions(s, 64 * 64, SHIM_DTYPE, 1, &t_max, &t_stats, &mx) == PF_OK && mx > 0.99 && mx < 1.0;   // max of 4096 uniform [0,1) values
+    }
+    LOG("SOLVER", ok ? LOG_INFO : LOG_ERROR, "run_tests: %s (the full suite is `python -m pytest tests -m gpu` in the solver's repository)", ok ? "OK" : "FAILED");
+    return ok;
 }
 
-extern "C" bool run_benchmarks(int N)
+// reference simulation.cu:1300-1358: median time and GiB/s of the max-reduction at six sizes (its CPU and thrust legs have no
+// counterpart here), printed in the reference's format; plus the five-statistics reduction of pf_step's do_stats.
+extern "C" bool run_benchmarks(int N_)
 {
-    (void) N;
-    fprintf(stderr, "run_benchmarks: use `python bench.py` of the B200 solver repository\n");
+    (void) N_;
+    const size_t Ns[] = {256 * 256, 512 * 512, 1024 * 1024, 2048 * 2048, 4096 * 4096, 2 * 4096 * 4096};
+    const int count = (int)(sizeof Ns / sizeof *Ns);
+    double t_max[8] = {0}, t_stats[8] = {0};
+    const double GiB = 1024.0 * 1024.0 * 1024.0;
+    pf_solver* s = solver_for(64, 64);
+    for(int i = 0; i < count; i++)
+    {
+        double mx = 0;
+        shim_check(s, pf_bench_reductions(s, Ns[i], PF_F32, 200, &t_max[i], &t_stats[i], &mx), "pf_bench_reductions");
+        printf("\n\nN:%i\nCUST: time: %e s | %4.2lf GB/s   (max |x| of %zu floats)\nSTAT: time: %e s | %4.2lf GB/s   (sum, L1, L2, min, max of a - b, 2 x %zu floats)\n",
+               (int) Ns[i], t_max[i], Ns[i] * 4 / GiB / t_max[i], Ns[i], t_stats[i], 2 * Ns[i] * 4 / GiB / t_stats[i], Ns[i]);
+    }
+    printf("cust_f32 = [");
+    for(int i = 0; i < count; i++) printf("(%e, %4.2lf), ", t_max[i], Ns[i] * 4 / GiB / t_max[i]);
+    printf("]\nstats_f32 = [");
+    for(int i = 0; i < count; i++) printf("(%e, %4.2lf), ", t_stats[i], 2 * Ns[i] * 4 / GiB / t_stats[i]);
+    printf("]\n");
     return true;
 }

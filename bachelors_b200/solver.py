@@ -21,7 +21,7 @@ EXPORTS = [
     "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
     "pf_step", "pf_step_host", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
-    "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches",
+    "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches", "pf_bench_reductions",
     "pf_init_fields", "pf_snapshot_begin", "pf_snapshot_wait", "pf_write_maps_bin", "pf_write_maps_bin_header",
     "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
     "pf_si_begin_async", "pf_si_partials", "pf_si_cg_begin_async", "pf_si_cg_spmv_async", "pf_si_cg_update_async",
@@ -76,6 +76,7 @@ def lib():
         "pf_stats_delta": (i32, [vp, vp, vp, P(pf_delta_stats)]),
         "pf_halo_region": (i32, [vp, vp, i32, P(vp), P(vp), P(sz)]),
         "pf_kernel_launches": (i64, [vp]),
+        "pf_bench_reductions": (i32, [vp, sz, i32, i32, P(dbl), P(dbl), P(dbl)]),
         "pf_init_fields": (i32, [vp, P(pf_params), P(pf_initial), vp, vp]),
         "pf_snapshot_begin": (i32, [vp, i32, i32, P(vp)]), "pf_snapshot_wait": (i32, [vp, i32, P(vp)]),
         "pf_write_maps_bin": (i32, [C.c_char_p, i32, i32, dbl, dbl, i64, dbl, i32, P(C.c_char_p), P(vp)]),
@@ -248,6 +249,12 @@ class Solver:
         out = pf_delta_stats()
         self._ck(lib().pf_stats_delta(self._h, a, b, C.byref(out)))
         return out
+
+    def bench_reductions(self, n, value_dtype=PF_F32, reps=50):
+        """-> (seconds of max|x| over n values, seconds of the five delta statistics over 2n values, the maximum)."""
+        a, b, m = C.c_double(0), C.c_double(0), C.c_double(0)
+        self._ck(lib().pf_bench_reductions(self._h, n, value_dtype, reps, C.byref(a), C.byref(b), C.byref(m)))
+        return a.value, b.value, m.value
 
     # -- rows around the stepping path (SURVEY section 8f)
     def init_fields(self, params, init, F, U):

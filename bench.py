@@ -120,6 +120,23 @@ def workload(args, world):
     return cfg, f"synthetic {args.solver} {p.nx}x{p.ny} ({args.dtype}), {PER_GPU_ROWS}-row slab per GPU"
 
 
+def config_dict(args, world, p, desc, rs):
+    """`config` of the JSON line: identical in both arms (the driver compares them)."""
+    return {"workload": desc, "solver": args.solver, "nx": p.nx, "ny": p.ny, "parallelism": f"y-slabs x{world}",
+            "l2_policy": ("working set (2 fields in + 2 out) %.0f MB per GPU vs 126 MB L2; consecutive time steps, no flush"
+                          % (4 * rs * p.nx * p.ny / world / 1e6)),
+            "halo_overlap": (not args.no_overlap) if world > 1 else None}
+
+
+def load_inst_counts(solver, dtype_name, size):
+    """Executed warp instructions per launch of the dominant kernel from the committed ncu capture (profiles/inst_counts.json)."""
+    path = os.path.join(ROOT, "profiles", "inst_counts.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f).get(f"{solver}_{dtype_name}_{size}")
+    return None
+
+
 # ------------------------------------------------------------------------------------------------------------------------------
 # reference arm: the CPU oracle port (the reference has no CPU implementation of this path, see DESIGN.md "Oracle")
 # ------------------------------------------------------------------------------------------------------------------------------
@@ -160,17 +177,26 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     dtype = PF_F64 if args.dtype == "f64" else PF_F32
-    cfg, desc = workload(args, 1)
-    if world > 1:                                # the CUDA arm's workload at this N; the sample below is a window of the same cells (same dx, dy, seed)
-        desc = workload(args, world)[1]
-    # bounded sample per step: a centred 724^2 window (1/8 of the 2048^2 cells, same dx/dy) so that K steps end within minutes
-    w = 724
+    rs = 8 if dtype == PF_F64 else 4
+    cfg_job, desc = workload(args, world)              # the CUDA arm's workload at this N: the line's config
     from oracle.oracle import Oracle, lib as olib
     # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its workers, and at N > 1 rank 0 is the
     # only rank that works in this arm
     olib().orc_set_threads(len(os.sched_getaffinity(0)))
     cores = olib().orc_max_threads()
-    p, F, U = cpu_window(cfg, dtype, w)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    if world == 1:
+        # the WHOLE grid of the workload every step (2048^2: ~60 ms per explicit-rk4 step on 16 cores)
+        p = cfg_job.params.copy()
+        F, U = make_initial_conditions(cfg_job, npdt)
+        what = f"each step = one {args.solver} step of the whole {p.nx}x{p.ny} grid of the workload"
+    else:
+        # bounded sample per step: ONE rank's slab of the job (16384 x 2048 cells = 1/N of the cells, the same arithmetic per cell)
+        wide = argparse.Namespace(**vars(args)); wide.wide = True
+        cfg1, _ = workload(wide, 1)
+        p = cfg1.params.copy()
+        F, U = make_initial_conditions(cfg1, npdt)
+        what = f"each step = one {args.solver} step of one rank's {p.nx}x{p.ny} slab (1/{world} of the job's cells)"
     o = Oracle(dtype, p.nx, p.ny)
     for _ in range(max(args.warmup, 1)):
         F, U, _, _ = o.step(p, F, U)
@@ -179,13 +205,14 @@ def run_reference_arm(args):
         F, U, _, _ = o.step(p, F, U)
     secs = time.perf_counter() - t0
     glups = p.nx * p.ny * args.steps / secs / 1e9
-    sample = f"each step = one {args.solver} step on the centred {w}x{w} window of the 2048^2 dendrite config (same dx, dy), {cores} OpenMP threads"
+    sample = f"{what}, {cores} OpenMP threads"
     line = {
         "impl": "reference", "metric": "GLUPS", "value": glups, "unit": "1e9 cell updates/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": args.dtype, "data": "synthetic (config's dendrite seed)",
-        "config": {"workload": desc, "solver": args.solver, "note": "the reference has no CPU implementation of this path (CUDA only); "
-                   "this arm times the CPU oracle port of it (oracle/, C + OpenMP) on the host cores"},
+        "dtype": args.dtype, "data": "synthetic (config's dendrite seed; no dataset)",
+        "config": config_dict(args, world, cfg_job.params, desc, rs),
+        "note": "the reference has no CPU implementation of this path (CUDA only); this arm times the CPU oracle port of it "
+                "(oracle/, C + OpenMP) on the host cores",
         "cpu_baseline": {"value": glups, "unit": "1e9 cell updates/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": glups, "unit": "1e9 cell updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -334,7 +361,7 @@ def run_cuda_arm(args):
         # the "launch" of the roofline is the whole step (prepare + both solves)
         cg_per_step = runner.cg_iters_total / max(args.steps, 1)
         alg_per_cell = (4 + 10 * cg_per_step) * rs
-        achieved = alg_per_cell * cells / (ms * 1e-3 / args.steps) / 1e9
+        achieved = alg_per_cell * (cells / world) / (ms * 1e-3 / args.steps) / 1e9       # per GPU, against one GPU's peak
         kernel_name = ("k_si_step_coop (whole step in one cooperative launch)" if world == 1
                        else "k_si_prepare + k_cg_spmv/update/pupdate (whole step, phase API)")
     traffic = load_traffic(args.solver, args.dtype, p.nx) if world == 1 and not args.wide and args.field == "seed" else None
@@ -353,10 +380,7 @@ def run_cuda_arm(args):
         "metric": "GLUPS", "value": glups, "unit": "1e9 cell updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": ("synthetic (config's dendrite seed; no dataset)" if args.field == "seed" else f"synthetic ({args.field} field of SURVEY 8d; no dataset)"),
-        "config": {"workload": desc, "solver": args.solver, "nx": p.nx, "ny": p.ny, "parallelism": f"y-slabs x{world}",
-                   "l2_policy": ("working set (2 fields in + 2 out) %.0f MB per GPU vs 126 MB L2; consecutive time steps, no flush"
-                                 % (4 * rs * cells / world / 1e6)),
-                   "halo_overlap": (not args.no_overlap) if world > 1 else None},
+        "config": config_dict(args, world, p, desc, rs),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": kernel_name, "peak_source": peak_src,
                      "algorithmic_bytes_per_cell_step": alg_per_cell, "launches_per_step": launches_per_step},
@@ -366,11 +390,21 @@ def run_cuda_arm(args):
         "clocks": clocks,
         "sim_time_advanced": t_adv,
     }
+    sec = secondary_roofline(args, p, world, avg_launch_s, clocks, runner.solver)
+    if sec:
+        line["roofline_secondary"] = sec
     if args.solver == "explicit-rk4-adaptive":
         line["attempts_per_step"] = attempts / args.steps
     if args.solver == "semi-implicit":
         line["cg_iterations_per_step"] = runner.cg_iters_total / args.steps
 
+    if world > 1 and not args.no_parity:
+        line["parity_check"] = parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, local)
+    if world > 1 and not args.no_weak_base:
+        base = weak_base(args, dtype, torch, dist, rank, local)
+        if rank == 0:
+            line["weak_base"] = base
+            line["weak_efficiency"] = glups / (world * base["value"])
     if rank == 0 and world == 1 and not args.no_cpu:
         v, cores, sample = cpu_port_rate(cfg, dtype, budget_s=args.cpu_budget, max_steps=400, w=None if not args.wide else 2048)
         line["cpu_baseline"] = {"value": v, "unit": "1e9 cell updates/s", "cores": cores, "kind": "port", "sample": sample}
@@ -385,6 +419,135 @@ def run_cuda_arm(args):
     if rank == 0:
         print(json.dumps(line), flush=True)
     return 0
+
+
+def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, local, steps=3):
+    """N > 1, after the timed region: the slabs and ONE GPU holding the whole grid each take `steps` steps from the same initial
+    state; every rank's owned rows must equal the single-grid rows bit for bit (compared on rank 0 as 64-bit integers, and by
+    SHA-256 of the 2 x ghost rows next to every slab boundary - the rows the halo exchange feeds)."""
+    import hashlib
+    from bachelors_b200 import solver as S
+    from bachelors_b200.distributed import SlabRunner
+    from bachelors_b200.slabs import slab_rows
+    p = cfg.params
+    fresh = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap)
+    fresh.upload_global(F0, U0)
+    dev = torch.device("cuda", local)
+    tdt = torch.float64 if dtype == PF_F64 else torch.float32
+    full = None
+    if rank == 0:
+        full = [torch.empty((p.ny, p.nx), dtype=tdt, device=dev) for _ in range(4)]
+    # the initial state of the whole grid, gathered on rank 0 from the slabs' owned rows
+    for f_i, t in enumerate((fresh.F, fresh.U)):
+        own = fresh.owned(t).contiguous()
+        if rank == 0:
+            y0, y1 = slab_rows(p.ny, world, 0)
+            full[f_i][y0:y1].copy_(own)
+            for r in range(1, world):
+                y0, y1 = slab_rows(p.ny, world, r)
+                dist.recv(full[f_i][y0:y1], src=r)
+        else:
+            dist.send(own, dst=0)
+    for _ in range(steps):
+        fresh.step()
+    fresh.sync()
+    ok, digests, worst_rel = True, [], 0.0
+    if rank == 0:
+        with S.Solver(p.nx, p.ny, dtype, device=local) as one:
+            q = p.copy()
+            F, U, nF, nU = (t.data_ptr() for t in full)
+            cur = [0, 1, 2, 3]
+            for i in range(steps):
+                q.iter, q.time = i, i * p.dt
+                one.step(q, full[cur[0]].data_ptr(), full[cur[1]].data_ptr(), full[cur[2]].data_ptr(), full[cur[3]].data_ptr())
+                cur = [cur[2], cur[3], cur[0], cur[1]]
+            one.sync()
+        ref_F, ref_U = full[cur[0]], full[cur[1]]
+    itype = torch.int64 if dtype == PF_F64 else torch.int32
+    g = max(runner.ghost, 1) * 2
+    for f_i, t in enumerate((fresh.F, fresh.U)):
+        own = fresh.owned(t).contiguous()
+        if rank == 0:
+            ref = ref_F if f_i == 0 else ref_U
+            buf = torch.empty_like(own)
+            for r in range(world):
+                y0, y1 = slab_rows(p.ny, world, r)
+                got = own if r == 0 else buf[:y1 - y0]
+                if r:
+                    dist.recv(got, src=r)
+                want = ref[y0:y1]
+                if args.solver == "semi-implicit":
+                    # the CG dot products are summed in another order on slabs: parity by north_star's tolerance, not by bits
+                    rel = float(torch.linalg.vector_norm((got - want).double()) / torch.linalg.vector_norm(want.double()).clamp_min(1e-300))
+                    worst_rel = max(worst_rel, rel)
+                    continue
+                ok = ok and bool(torch.equal(got.view(itype), want.view(itype)))
+                for a, b in ((y0, min(y0 + g, y1)), (max(y1 - g, y0), y1)):
+                    hg = hashlib.sha256(got[a - y0:b - y0].cpu().numpy().tobytes()).hexdigest()
+                    hw = hashlib.sha256(want[a - y0:b - y0].cpu().numpy().tobytes()).hexdigest()
+                    ok = ok and hg == hw
+                    digests.append(hg[:16])
+        else:
+            dist.send(own, dst=0)
+    fresh.close()
+    del full
+    torch.cuda.empty_cache()
+    dist.barrier()
+    if rank != 0:
+        return None
+    if args.solver == "semi-implicit":
+        tol = 1e-10 if dtype == PF_F64 else 1e-5
+        return {"steps": steps, "bit_identical": False, "rel_l2": worst_rel, "within_tolerance": worst_rel <= tol, "tolerance": tol, "ranks": world,
+                "what": f"{steps} steps on {world} slabs vs the whole grid on rank 0's GPU: worst relative L2 difference over fields and slabs "
+                        "(the CG dot products are summed in another order on slabs)"}
+    return {"steps": steps, "bit_identical": bool(ok), "ranks": world,
+            "what": f"{steps} steps of the {p.nx}x{p.ny} grid on {world} slabs vs the whole grid on rank 0's GPU: all owned rows compared as "
+                    f"integers on the device; SHA-256 of the {g} rows at both ends of every slab (first 16 hex digits below)",
+            "sha256_boundary_rows": digests}
+
+
+def weak_base(args, dtype, torch, dist, rank, local):
+    """N > 1: ONE rank's workload (the 16384 x 2048 slab) timed alone on rank 0's GPU in the same run: the base the weak-scaling
+    efficiency is measured against (the driver's N = 1 line is the 2048^2 config, a different per-GPU workload)."""
+    from bachelors_b200.distributed import SlabRunner
+    out = None
+    if rank == 0:
+        wide = argparse.Namespace(**vars(args)); wide.wide = True
+        cfg1, desc1 = workload(wide, 1)
+        p1 = cfg1.params
+        npdt = np.float64 if dtype == PF_F64 else np.float32
+        F1, U1 = make_initial_conditions(cfg1, npdt)
+        r1 = SlabRunner(p1, dtype, rank=0, world=1, device=local)
+        r1.upload_global(F1, U1)
+        for _ in range(args.warmup):
+            r1.step()
+        r1.sync()
+        ms, _, _ = time_device_steps(r1, torch, args.steps, 1, dist)
+        out = {"value": p1.nx * p1.ny * args.steps / (ms * 1e-3) / 1e9, "ms_per_step": ms / args.steps, "workload": desc1 + ", rank 0 alone, same run"}
+        r1.close()
+    dist.barrier()
+    return out
+
+
+def secondary_roofline(args, p, world, avg_launch_s, clocks, solver):
+    """The ceilings that bind the multi-stage kernels: FP64 pipe and issue slots. Executed warp instructions
+    per launch come from the committed ncu capture of the same kernel and grid (profiles/inst_counts.json); the FP64 peak is the
+    rate measured on this pool's B200 with tools/ubench_fp64.cu (profiles/r02_kernel_experiments.md section 4)."""
+    if world != 1 or args.wide or args.field != "seed":
+        return None
+    ic = load_inst_counts(args.solver, args.dtype, p.nx)
+    if not ic:
+        return None
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    sms = 148
+    clk = avg_launch_s * mhz * 1e6                                         # SM cycles per launch
+    fp64 = ic["fp64_warp_inst"] / (clk * sms)                              # warp instructions / clk / SM
+    issue = ic["warp_inst"] / (clk * sms * 4)                              # warp instructions / clk / scheduler
+    return [
+        {"bound": "fp64_pipe", "achieved": fp64, "peak": ic.get("fp64_peak_per_clk_sm", 1.9), "unit": "FP64 warp-instructions/clk/SM",
+         "frac": fp64 / ic.get("fp64_peak_per_clk_sm", 1.9), "source": ic.get("source")},
+        {"bound": "issue", "achieved": issue, "peak": 1.0, "unit": "warp-instructions/clk/scheduler", "frac": issue, "source": ic.get("source")},
+    ]
 
 
 def same_box_reference(cfg, dtype, args):
@@ -422,6 +585,8 @@ def main():
     ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
     ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the 3-step bit comparison against the whole grid on one GPU")
+    ap.add_argument("--no-weak-base", action="store_true", help="N > 1: skip timing one rank's slab alone on rank 0")
     ap.add_argument("--no-ref-gpu", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=20)

@@ -340,6 +340,14 @@ PF_API int  pf_render_rgba(pf_solver* s, const void* dev_field, float display_mi
 /* Minimal PNG writer (8-bit RGBA, stored deflate blocks). flip_y != 0 puts grid row 0 at the bottom, as the viewer does. */
 PF_API int  pf_write_png(const char* path, int width, int height, const uint8_t* rgba, int flip_y);
 
+/* ---- reduction micro-benchmark: replaces run_benchmarks (simulation.cu:1300-1358, numbers in its plot.py:731-733) -------------
+ * Times, on the solver's stream with CUDA events (median of `reps` after two warm-up rounds), this library's two reductions over
+ * n pseudo-random values of value_dtype: (1) max |x| - 16-byte loads, warp shuffles, one integer atomicMax per warp on the IEEE bit
+ * pattern, what replaces the reference's multi-pass cuda_reduce(Reduce::MAX); reads n values; (2) the five delta statistics of a - b
+ * (cuda_stats_delta, cuda_reduction.cuh:391-407) as pf_step computes them; reads 2n values. *max_value returns the reduced maximum
+ * (< 1, the generator is uniform in [0, 1)). */
+PF_API int  pf_bench_reductions(pf_solver* s, size_t n, int value_dtype, int reps, double* seconds_max, double* seconds_stats, double* max_value);
+
 /* ---- counters -------------------------------------------------------------------------------- */
 PF_API int64_t pf_kernel_launches(const pf_solver* s);      /* kernels launched by this solver so far (bench.py: gpu_launches) */
 

@@ -29,9 +29,16 @@ def test_reference_arm_line_without_a_gpu():
     assert d["metric"] == "GLUPS" and d["higher_is_better"] is True and d["vs_baseline"] is None and d["n_gpus"] == 1
     assert d["value"] > 0 and d["ms_per_step"] > 0 and d["steps"] == 2
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["value"] == d["value"] and cb["cores"] == len(os.sched_getaffinity(0)) and "724x724" in cb["sample"]
+    assert cb["kind"] == "port" and cb["value"] == d["value"] and cb["cores"] == len(os.sched_getaffinity(0))
+    assert "whole 2048x2048 grid" in cb["sample"]                       # the same configuration as the CUDA arm at N = 1, not a window
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert "workload" in d["config"] and "model" not in d["config"]
+    # both arms print the same `config` (the driver compares them): what the CUDA arm would print for this command line
+    import argparse
+    import bench
+    args = argparse.Namespace(solver="explicit-rk4", dtype="f64", size=0, wide=False, no_overlap=False)
+    cfg, desc = bench.workload(args, 1)
+    assert d["config"] == bench.config_dict(args, 1, cfg.params, desc, 8)
 
 
 def test_reference_arm_other_ranks_exit_without_work():
@@ -53,6 +60,8 @@ def test_cuda_arm_line():
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-12 and 0 < r["frac"] < 1
     assert abs(r["achieved"] - 32 * cells / (d["ms_per_step"] * 1e-3) / 1e9) <= 1e-6 * r["achieved"]     # 4 s bytes per cell, fp64
     assert r["traffic"] is None or r["traffic"] > 0
+    sec = {x["bound"]: x for x in d["roofline_secondary"]}               # the ceilings that bind RK4: FP64 pipe and issue slots
+    assert set(sec) == {"fp64_pipe", "issue"} and all(0 < x["frac"] < 1 and abs(x["frac"] - x["achieved"] / x["peak"]) < 1e-12 for x in sec.values())
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["value"] > 0 and cb["cores"] >= 1 and cb["sample"]
     e = d["e2e"]

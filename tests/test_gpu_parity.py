@@ -270,6 +270,34 @@ def test_run_equals_repeated_steps_and_is_bit_stable(solver):
     assert len(digests) == 1
 
 
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("bc", ["neumann", "periodic", "dirichlet"])
+@pytest.mark.parametrize("solver,size,steps", [("explicit-rk4", (200, 136), 7), ("explicit-rk4", (512, 512), 12), ("explicit", (333, 257), 9),
+                                               ("explicit", (1024, 1024), 6), ("explicit-rk4", (2048, 2048), 5), ("explicit-rk4", (37, 64), 4)])
+def test_run_is_one_multi_step_launch_with_the_bits_of_single_steps(solver, size, steps, bc, dtype):
+    """pf_run of the fixed-step explicit solvers = ONE cooperative launch that advances all the steps (k_stream_run: every
+    unit waits only for its 8 neighbouring tiles, no grid barrier, buffers swap roles every step): the same bits as `steps`
+    single-step launches, for odd and even step counts, every boundary type, grids of one and of many tiles."""
+    nx, ny = size
+    if size == (2048, 2048) and (bc != "neumann" or dtype != PF_F64):
+        pytest.skip("full size once")
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2 if nx < 1000 else 0.0, Phi_boundary=bc, T_boundary=bc)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    ref = cuda_replay(p, F0, U0, dtype, steps)
+    with S.Solver(nx, ny, dtype) as s:
+        F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        l0 = s.kernel_launches
+        Fo, Uo, done, t, info = s.run(p, F, U, tF, tU, steps)
+        assert s.kernel_launches - l0 == 1                   # the multi-step path really ran
+        assert done == steps and Fo == (tF if steps % 2 else F) and abs(t - ref[2]) <= 1e-15
+        assert np.array_equal(s.download(Fo), ref[0]) and np.array_equal(s.download(Uo), ref[1])
+        # a second run continues from the first one's state (the progress words are not reset between launches)
+        Fo2, Uo2, done2, _, _ = s.run(p, Fo, Uo, tF if Fo == F else F, tU if Uo == U else U, 3)
+        ref2 = cuda_replay(p, ref[0], ref[1], dtype, 3)
+        assert done2 == 3 and np.array_equal(s.download(Fo2), ref2[0]) and np.array_equal(s.download(Uo2), ref2[1])
+
+
 def test_run_stops_at_stop_time():
     nx = ny = 64
     p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=0.5)

@@ -148,3 +148,51 @@ def test_maps_are_zero_filled_resized_and_freed_like_the_reference():
             sim.upload(a, a * 2)
             F, U = sim.download(np.float32)
             assert np.array_equal(F, a) and np.array_equal(U, a * 2)
+
+
+def test_two_grid_sizes_live_at_once():
+    """sim_realloc frees and sim_modify* copies through the handle that OWNS a map (the shim's allocation table), so maps of
+    different sizes can be live, stepped and freed in any order."""
+    need_shim(PF_F64)
+    pa = default_params(solver="explicit-rk4", nx=144, ny=96, L0=144 / 128.0)
+    pb = default_params(solver="explicit-rk4", nx=208, ny=176, L0=208 / 128.0)
+    Fa, Ua = seeded_fields(pa.nx, pa.ny, np.float64, kind="interface")
+    Fb, Ub = seeded_fields(pb.nx, pb.ny, np.float64, kind="smooth")
+    wa = direct(pa, Fa, Ua, PF_F64, 3)
+    wb = direct(pb, Fb, Ub, PF_F64, 3)
+    a = ref_sim.RefSim(PF_F64, pa.nx, pa.ny, impl="shim")
+    b = ref_sim.RefSim(PF_F64, pb.nx, pb.ny, impl="shim")          # now the NEWEST handle is b's
+    a.upload(Fa, Ua)                                                  # must go through a's handle
+    b.upload(Fb, Ub)
+    a.run(pa, 3); b.run(pb, 3)
+    gFa, gUa = a.download()
+    a.close()                                                         # frees a's maps while b's are live
+    gFb, gUb = b.download()
+    b.close()
+    assert np.array_equal(gFa, wa[0]) and np.array_equal(gUa, wa[1])
+    assert np.array_equal(gFb, wb[0]) and np.array_equal(gUb, wb[1])
+
+
+def test_run_tests_and_run_benchmarks_have_bodies(capfd):
+    """run_tests / run_benchmarks (reference simulation.h:143-144): the reduction micro-benchmark at the reference's six sizes."""
+    need_shim(PF_F32)
+    import ctypes
+    L = ref_sim.load(PF_F32, impl="shim")
+    L.run_tests.restype = ctypes.c_bool
+    L.run_benchmarks.restype = ctypes.c_bool
+    L.run_benchmarks.argtypes = [ctypes.c_int]
+    assert L.run_tests()
+    assert L.run_benchmarks(0)
+    out = capfd.readouterr().out
+    assert "cust_f32 = [" in out and out.count("N:") == 6
+
+
+def test_reduction_benchmark_values():
+    """pf_bench_reductions: the maximum of the hashed uniform sequence is just below 1; times are positive and ordered by size."""
+    with S.Solver(64, 64, PF_F64) as s:
+        t_small = s.bench_reductions(256 * 256, PF_F32, reps=5)
+        t_big = s.bench_reductions(4096 * 4096, PF_F32, reps=5)
+        assert 0.99 < t_small[2] < 1.0 and 0.999 < t_big[2] < 1.0
+        assert 0 < t_small[0] < t_big[0] and 0 < t_small[1] < t_big[1]
+        t64 = s.bench_reductions(1 << 20, PF_F64, reps=3)
+        assert 0.99 < t64[2] < 1.0

@@ -163,6 +163,56 @@ static void run_scheme(const char* sname, int nx, int ny, int reps, const std::v
     cudaFree(dF); cudaFree(dU); cudaFree(rF); cudaFree(rU); cudaFree(oF); cudaFree(oU); cudaFree(derr);
 }
 
+// n_steps time steps as n_steps single-step launches and as ONE multi-step launch (StreamRun): same bits, time per step of both.
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+static void run_multi(const char* sname, int nx, int ny, int n_steps, int nch, int bc, int kind, int reps)
+{
+    const size_t N = (size_t) nx * ny, bytes = N * sizeof(Real);
+    Real *dF, *dU, *aF, *aU, *bF, *bU; unsigned* prog;
+    CK(cudaMalloc(&dF, bytes)); CK(cudaMalloc(&dU, bytes)); CK(cudaMalloc(&aF, bytes)); CK(cudaMalloc(&aU, bytes)); CK(cudaMalloc(&bF, bytes)); CK(cudaMalloc(&bU, bytes));
+    std::vector<Real> hF, hU, wF(N), wU(N), gF(N), gU(N);
+    pf_params p = bench_params(nx, ny, bc, ANISO ? 0.3 : 0.0);
+    make_fields<Real>(kind, nx, ny, hF, hU);
+    constexpr int NST = SchemeStages<SCHEME>::value, EWI = 32 * WARPS - 2 * NST;
+    const size_t smem = stream_smem_bytes<Real, SCHEME, WARPS>();
+    auto kern = k_stream_step<Real, SCHEME, ANISO, WARPS, MINB>;
+    auto kern_run = k_stream_run<Real, SCHEME, ANISO, WARPS, MINB>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    CK(cudaFuncSetAttribute(kern_run, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    CK(cudaFuncSetAttribute(kern_run, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    FusedArgs<Real> a = make_args<Real>(p, aF, aU, bF, bU, SCHEME, nullptr);
+    a.strips = stream_strips(nx, EWI, NST, bc == PF_BOUNDARY_PERIODIC); a.nch = std::min(nch, ny);
+    const int units = a.strips * a.nch;
+    CK(cudaMalloc(&prog, (units + 1) * sizeof(unsigned))); CK(cudaMemset(prog, 0, (units + 1) * sizeof(unsigned)));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    auto reset = [&] { CK(cudaMemcpy(aF, hF.data(), bytes, cudaMemcpyHostToDevice)); CK(cudaMemcpy(aU, hU.data(), bytes, cudaMemcpyHostToDevice)); };
+    auto single = [&](int n) { FusedArgs<Real> x = a;
+        for(int i = 0; i < n; i++) { kern<<<units, 32 * WARPS, smem>>>(x); std::swap(const_cast<Real*&>(x.F), x.out_F); std::swap(const_cast<Real*&>(x.U), x.out_U); } };
+    unsigned base = 1;
+    auto multi = [&](int n) { StreamRun r; r.n_steps = n; r.base = base; r.progress = prog; r.units = units; base += n;
+        FusedArgs<Real> x = a; void* args[] = {&x, &r};
+        CK(cudaLaunchCooperativeKernel((const void*) kern_run, dim3(units), dim3(32 * WARPS), args, smem, 0)); };
+    float ms1 = 0, msn = 0;
+    reset(); single(n_steps); CK(cudaDeviceSynchronize());
+    const Real* rF = (n_steps & 1) ? bF : aF; const Real* rU = (n_steps & 1) ? bU : aU;
+    CK(cudaMemcpy(wF.data(), rF, bytes, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(wU.data(), rU, bytes, cudaMemcpyDeviceToHost));
+    reset(); multi(n_steps); CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(gF.data(), rF, bytes, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(gU.data(), rU, bytes, cudaMemcpyDeviceToHost));
+    unsigned stalled = 0; CK(cudaMemcpy(&stalled, prog + units, 4, cudaMemcpyDeviceToHost));
+    size_t bad = 0;
+    for(size_t i = 0; i < N; i++) if(memcmp(&gF[i], &wF[i], sizeof(Real)) || memcmp(&gU[i], &wU[i], sizeof(Real))) bad++;
+    for(int rep = 0; rep < reps; rep++)
+    {
+        CK(cudaEventRecord(e0)); single(n_steps); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); float m; CK(cudaEventElapsedTime(&m, e0, e1)); ms1 = rep ? std::min(ms1, m) : m;
+        CK(cudaEventRecord(e0)); multi(n_steps); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaEventElapsedTime(&m, e0, e1)); msn = rep ? std::min(msn, m) : m;
+    }
+    printf("%-6s %-4s %dx%d bc=%d kind=%d nch=%d units=%d steps=%d: per step %8.2f us (single launches) %8.2f us (one launch)  %s%s\n", sname, sizeof(Real) == 8 ? "f64" : "f32",
+           nx, ny, bc, kind, a.nch, units, n_steps, ms1 * 1e3 / n_steps, msn * 1e3 / n_steps, bad ? "MISMATCH" : "BITEXACT", stalled ? " STALLED" : "");
+    fflush(stdout);
+    cudaFree(dF); cudaFree(dU); cudaFree(aF); cudaFree(aU); cudaFree(bF); cudaFree(bU); cudaFree(prog);
+}
+
 #define V(Real, SCHEME, ANISO, W, MB, CH) Variant<Real>{ "stream w" #W " b" #MB " nch" #CH, launch_stream<Real, SCHEME, ANISO, W, MB>, CH }
 
 #ifdef KB_VARIANTS_FILE
