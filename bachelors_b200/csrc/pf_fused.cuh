@@ -45,6 +45,9 @@ struct FusedArgs {
     //  RKM (simulation.cu:406-409, :472): w[0]=tau/3 w[1]=tau/6 w[2]=tau/8 w[3]=tau*3/8 w[4]=tau/2 w[5]=-tau*3/2 w[6]=tau*2 w[7]=tau/6
     Real w[8];
     unsigned long long* err_bits;      // RKM: [0] = max|e_Phi| bits, [1] = max|e_T| bits (atomicMax)
+    // RKM, one launch per attempt (pf_stream.cuh): the last unit to finish hands the two norms and err_seq to the host through
+    // mapped pinned memory (err_host[0..2]) and re-arms err_bits / err_ticket; NULL: the words stay on the device for the caller
+    unsigned long long* err_host; unsigned* err_ticket; unsigned long long err_seq;
 };
 
 template <int SCHEME> struct SchemeStages { static constexpr int value = SCHEME == SCHEME_EULER ? 1 : (SCHEME == SCHEME_RK4 ? 4 : 5); };

@@ -20,6 +20,7 @@
 #include "pf_general.cuh"
 #include "pf_si_coop.cuh"
 #include "pf_app.cuh"
+#include "pf_halo.cuh"
 
 using namespace pf;
 
@@ -39,7 +40,10 @@ struct pf_solver {
     void* partials = nullptr;               // 4 x CG_MAX_BLOCKS reals (as doubles)
     CgState* d_cg = nullptr;                // [2]: Phi solve, T solve
     StatsPartial* d_stats = nullptr;        // CG_MAX_BLOCKS
-    unsigned long long* d_err = nullptr;    // [2]
+    unsigned long long* d_err = nullptr;    // [2] error-norm bit patterns + (as unsigned) the arrival ticket in word [2]
+    bool d_err_dirty = true;                // the words may be non-zero (the hand-over path needs them zero and leaves them zero)
+    unsigned long long* h_mail = nullptr;   // [3] mapped pinned: {max|e_Phi| bits, max|e_T| bits, sequence number} written by the attempt kernel
+    unsigned long long mail_seq = 0;
     void* staging = nullptr; size_t staging_bytes = 0;
 
     // pinned host mirrors
@@ -67,6 +71,7 @@ struct pf_solver {
     int host_bands = 8;                     // PF_OPT_HOST_BANDS: row bands of the pipelined pf_step_host
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
+    bool rkm_handover = false;              // rk4_adaptive_step: the attempt kernel mails its norms to the host (see FusedArgs::err_host)
     int win_y0 = 0, win_y1 = 0;             // row window of the *_rows_async entry points (global rows); empty = all owned rows
     cudaStream_t aux_stream = nullptr;      // second stream: boundary rows of a slab run here while the interior runs on `stream`
     cudaStream_t launch_stream = nullptr;   // stream the next fused launch goes to (stream or aux_stream)
@@ -81,6 +86,7 @@ struct pf_solver {
     void* d_rgba = nullptr; size_t rgba_bytes = 0;      // pf_render_rgba
     // pf_si_*: the semi-implicit step in phases (slabs); what pf_si_begin_async was given
     struct SiCtx { pf_params p; const void *F = nullptr, *U = nullptr, *U_base = nullptr; void *nF = nullptr, *nU = nullptr; bool active = false; } si;
+    unsigned* halo_flags = nullptr;         // device-initiated halo exchange (pf_halo.cuh): words the neighbours write through peer mappings
     int64_t launches = 0;
     std::string err;
 
@@ -190,13 +196,22 @@ int pf_create_slab(pf_solver** out, int device, int dtype, int nx, int ny_global
     PF_CREATE_CUDA(cudaSetDevice(device));
     PF_CREATE_CUDA(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
     PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    PF_CREATE_CUDA(cudaStreamCreateWithFlags(&s->aux_stream, cudaStreamNonBlocking));
+    {
+        // the auxiliary stream carries a slab's edge rows and their hand-over to the neighbours: its small kernels must get SM slots
+        // ahead of the interior's CTAs
+        int prio_lo = 0, prio_hi = 0;
+        PF_CREATE_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        PF_CREATE_CUDA(cudaStreamCreateWithPriority(&s->aux_stream, cudaStreamNonBlocking, prio_hi));
+    }
     PF_CREATE_CUDA(cudaMalloc(&s->partials, 4 * CG_MAX_BLOCKS * sizeof(double)));
     PF_CREATE_CUDA(cudaMalloc(&s->ll_slots, (4 * CG_MAX_BLOCKS + 4) * sizeof(unsigned long long)));   // GridSum: 2 sets x 2 words per block + 2 x 2 result words
     PF_CREATE_CUDA(cudaMemset(s->ll_slots, 0, (4 * CG_MAX_BLOCKS + 4) * sizeof(unsigned long long)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_cg, 2 * sizeof(CgState)));
     PF_CREATE_CUDA(cudaMalloc((void**) &s->d_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
-    PF_CREATE_CUDA(cudaMalloc((void**) &s->d_err, 2 * sizeof(unsigned long long)));
+    PF_CREATE_CUDA(cudaMalloc((void**) &s->d_err, 3 * sizeof(unsigned long long)));
+    PF_CREATE_CUDA(cudaMemset(s->d_err, 0, 3 * sizeof(unsigned long long)));
+    PF_CREATE_CUDA(cudaHostAlloc((void**) &s->h_mail, 3 * sizeof(unsigned long long), cudaHostAllocMapped));
+    memset(s->h_mail, 0, 3 * sizeof(unsigned long long));
     PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_err, 2 * sizeof(unsigned long long)));
     PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_cg, 2 * sizeof(CgState)));
     PF_CREATE_CUDA(cudaMallocHost((void**) &s->h_stats, CG_MAX_BLOCKS * sizeof(StatsPartial)));
@@ -220,11 +235,13 @@ void pf_destroy(pf_solver* s)
     if(s->partials) cudaFree(s->partials);
     if(s->ll_slots) cudaFree(s->ll_slots);
     if(s->run_progress) cudaFree(s->run_progress);
+    if(s->halo_flags) cudaFree(s->halo_flags);
     if(s->d_cg) cudaFree(s->d_cg);
     if(s->d_stats) cudaFree(s->d_stats);
     if(s->d_err) cudaFree(s->d_err);
     if(s->staging) cudaFree(s->staging);
     if(s->h_err) cudaFreeHost(s->h_err);
+    if(s->h_mail) cudaFreeHost(s->h_mail);
     if(s->h_cg) cudaFreeHost(s->h_cg);
     if(s->h_stats) cudaFreeHost(s->h_stats);
     if(s->aux_stream) { cudaStreamSynchronize(s->aux_stream); cudaStreamDestroy(s->aux_stream); }
@@ -465,13 +482,14 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
     const int max_n = std::max(1, rows / 4);
     for(int n = 1; n <= max_n; n++)
     {
-        const int chunk = (rows + n - 1) / n;
-        const long long ctas = (long long) strips * n;
+        const int chunk = (rows + n - 1) / n;                         // the longest chunk sets the time
+        const int nch = (rows + chunk - 1) / chunk;                   // the fewest chunks that are no longer than that
+        const long long ctas = (long long) strips * nch;
         const long long full = ctas / slots, rest = ctas % slots;
         const double its = chunk + fill + 3.0;                       // the checked first/last groups run slower
         const double occ_rest = std::min<double>(minb, std::ceil((double) rest / sm_count));
         const double cost = its * (full * (0.6 + 0.145 * minb) + (rest ? 0.6 + 0.145 * occ_rest : 0.0));
-        if(cost < best) { best = cost; best_n = n; }
+        if(cost < best) { best = cost; best_n = nch; }
     }
     return best_n;
 }
@@ -483,14 +501,18 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
     auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
-    auto kern_run = k_stream_run<Real, SCHEME, ANISO, W, MINB>;
+    constexpr bool HAS_RUN = SCHEME == SCHEME_RK4;                          // the only scheme with a multi-step kernel (see below)
     const size_t smem = stream_smem_bytes<Real, SCHEME, W>();
     if(!(s->stream_attr_done & (1u << inst_bit)))
     {
         PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        if constexpr (HAS_RUN)
+        {
+            auto kern_run = k_stream_run<Real, SCHEME, ANISO, W, MINB>;
+            PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+            PF_CUDA(s, cudaFuncSetAttribute(kern_run, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        }
         s->stream_attr_done |= 1u << inst_bit;
     }
     const int own_rows = a.own_y1 - a.own_y0;
@@ -500,9 +522,13 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     a.nch = stream_chunks(s->sm_count, MINB, a.strips, own_rows, StreamGeom<SCHEME>::FILL);
     const long long units = (long long) a.strips * a.nch;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
-    if(s->run_steps > 1 && SCHEME != SCHEME_RKM)
+    // Multi-step launch (pf_run). Measured on B200 against single-step launches (tools/kbench.cu run_multi, fp64): explicit-rk4
+    // 2048^2 -1 %, 1024^2 -2 %, 512^2 -10 %, 256^2 -6 %; the one-stage Euler step gains nothing from it (2048^2 +1 %, 512^2 +28 %:
+    // the neighbour hand-shake costs what the launch gap costs), so it keeps its single-step launches.
+    if constexpr (HAS_RUN) if(s->run_steps > 1)
     {
-        // Multi-step launch (pf_run): every unit must be resident at once and a tile may only depend on its 8 neighbours.
+        // every unit must be resident at once and a tile may only depend on its 8 neighbours
+        auto kern_run = k_stream_run<Real, SCHEME, ANISO, W, MINB>;
         if(!s->stream_resident[inst_bit])
         {
             int coop = 0, per_sm = 0;
@@ -511,13 +537,10 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
             s->stream_resident[inst_bit] = coop && per_sm > 0 ? per_sm : -1;
         }
         const bool whole_grid = s->is_full_grid() && s->win_y1 <= s->win_y0;
-        // one wave, and chunks of at least 2 x NST rows (a tile then only depends on its 8 neighbours): fewer chunks if need be
+        // one wave, and chunks of at least 2 x NST rows (a tile then only depends on its 8 neighbours)
         const long long slots = s->stream_resident[inst_bit] > 0 ? (long long) s->stream_resident[inst_bit] * s->sm_count : 0;
-        const int nch_run = (int) std::min<long long>({(long long) a.nch, (long long)(own_rows / (2 * NST)), slots / a.strips});
-        if(whole_grid && nch_run >= 1)
+        if(whole_grid && units <= slots && own_rows / a.nch >= 2 * NST)
         {
-            a.nch = nch_run;
-            const long long units = (long long) a.strips * a.nch;
             if(s->run_progress_units < units)
             {
                 if(s->run_progress) { PF_CUDA(s, cudaStreamSynchronize(s->stream)); PF_CUDA(s, cudaFree(s->run_progress)); s->run_progress = nullptr; }
@@ -678,6 +701,13 @@ template <typename Real> static Real decode_err(unsigned long long bits);
 template <> double decode_err<double>(unsigned long long bits) { double d; memcpy(&d, &bits, 8); return d; }
 template <> float decode_err<float>(unsigned long long bits) { uint32_t u = (uint32_t) bits; float f; memcpy(&f, &u, 4); return f; }
 
+static inline void pf_cpu_relax()
+{
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+}
+
 static inline double pf_pow(double a, double b) { return pow(a, b); }
 static inline float pf_pow(float a, float b) { return powf(a, b); }
 
@@ -709,10 +739,19 @@ template <typename Real>
 static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
 {
     const Real tau = (Real) tau_d;
-    if(!s->rkm_keep_errors) PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 2 * sizeof(unsigned long long), s->stream));
+    // (the tiled kernel that serves do_corrector_guess keeps the words on the device)
+    const bool handover = s->rkm_handover && s->rkm_fused && !s->rkm_keep_errors && !p.do_corrector_guess && s->is_full_grid() && s->win_y1 <= s->win_y0;
+    if(handover ? s->d_err_dirty : !s->rkm_keep_errors) PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 3 * sizeof(unsigned long long), s->stream));
+    s->d_err_dirty = !handover;
     if(s->rkm_fused)
     {
         FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+        if(handover)
+        {
+            unsigned long long* dev_mail = nullptr;
+            PF_CUDA(s, cudaHostGetDevicePointer((void**) &dev_mail, s->h_mail, 0));
+            a.err_host = dev_mail; a.err_ticket = (unsigned*)(s->d_err + 2); a.err_seq = ++s->mail_seq;
+        }
         a.w[0] = tau / 3; a.w[1] = tau / 6; a.w[2] = tau / 8; a.w[3] = tau * 3 / 8;
         a.w[4] = tau / 2; a.w[5] = -tau * 3 / 2; a.w[6] = tau * 2; a.w[7] = tau / 6;
         return launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a);
@@ -785,11 +824,38 @@ static int rk4_adaptive_step(pf_solver* s, const pf_params& p, const Real* F, co
     double used_tau = tau, eps_F = 0, eps_U = 0;
     for(; i < max_iters && !converged; i++)
     {
-        if(int rc = rkm_attempt<Real>(s, p, tau, F, U, nF, nU)) return rc;
-        PF_CUDA(s, cudaMemcpyAsync(s->h_err, s->d_err, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
-        PF_CUDA(s, cudaStreamSynchronize(s->stream));
+        s->rkm_handover = true;
+        const unsigned long long seq_before = s->mail_seq;
+        int rc = rkm_attempt<Real>(s, p, tau, F, U, nF, nU);
+        s->rkm_handover = false;
+        if(rc) return rc;
+        unsigned long long bits_F, bits_U;
+        if(s->mail_seq != seq_before)
+        {
+            // the kernel's last unit writes the norms into mapped host memory: spin on the sequence number (1-2 us after the
+            // kernel's end instead of ~10 for a copy + stream synchronisation)
+            volatile unsigned long long* m = s->h_mail;
+            for(unsigned long spins = 1; m[2] != s->mail_seq; spins++)
+            {
+                pf_cpu_relax();
+                if((spins & 0x3ffff) == 0)
+                {
+                    const cudaError_t q = cudaStreamQuery(s->stream);
+                    if(q == cudaSuccess && m[2] != s->mail_seq) { __sync_synchronize(); if(m[2] == s->mail_seq) break; return fail(s, PF_ERR_CUDA, "adaptive step: the attempt finished without reporting its error norms"); }
+                    if(q != cudaSuccess && q != cudaErrorNotReady) return fail(s, PF_ERR_CUDA, "adaptive step: %s", cudaGetErrorString(q));
+                }
+            }
+            __sync_synchronize();
+            bits_F = m[0]; bits_U = m[1];
+        }
+        else
+        {
+            PF_CUDA(s, cudaMemcpyAsync(s->h_err, s->d_err, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+            PF_CUDA(s, cudaStreamSynchronize(s->stream));
+            bits_F = s->h_err[0]; bits_U = s->h_err[1];
+        }
         used_tau = tau;
-        rkm_decide<Real>(p, used_tau, s->h_err[0], s->h_err[1], &converged, &stop, &tau, &eps_F, &eps_U);
+        rkm_decide<Real>(p, used_tau, bits_F, bits_U, &converged, &stop, &tau, &eps_F, &eps_U);
         if(stop == 2) break;                                                // :466: `break` skips the loop's i++
     }
     if(int rc = rkm_finish<Real>(s, used_tau, F, U, nF, nU)) return rc;
@@ -1433,3 +1499,4 @@ int pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* o
 
 #include "pf_app_host.inl"
 #include "pf_si_slab.inl"
+#include "pf_halo.inl"

@@ -462,6 +462,24 @@ __device__ __forceinline__ void stream_unit(const FusedArgs<Real>& a, const Real
             if(eF > 0) atomic_max_nonneg(a.err_bits + 0, eF);
             if(eT > 0) atomic_max_nonneg(a.err_bits + 1, eT);
         }
+        if(a.err_host)
+        {
+            // the host's step-size controller spins on err_host[2] instead of a device-to-host copy + stream synchronisation
+            __syncthreads();
+            if(cx == 0)
+            {
+                __threadfence();                                            // this unit's atomics before its ticket
+                if(atomicAdd(a.err_ticket, 1u) == (unsigned)(a.strips * a.nch) - 1u)
+                {
+                    const unsigned long long e0 = atomicExch(a.err_bits + 0, 0ull), e1 = atomicExch(a.err_bits + 1, 0ull);
+                    *a.err_ticket = 0;
+                    volatile unsigned long long* h = a.err_host;
+                    h[0] = e0; h[1] = e1;
+                    __threadfence_system();
+                    h[2] = a.err_seq;
+                }
+            }
+        }
     }
 }
 

@@ -332,7 +332,7 @@ def run_cuda_arm(args):
         F0, U0 = np.ascontiguousarray(gF[y0:y1]), np.ascontiguousarray(gU[y0:y1])
         desc += f", field = {args.field}"
 
-    runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap)
+    runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap, p2p=not args.no_p2p)
     runner.upload_global(F0, U0)
     launches0 = runner.solver.kernel_launches
     for _ in range(args.warmup):
@@ -430,7 +430,7 @@ def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, loc
     from bachelors_b200.distributed import SlabRunner
     from bachelors_b200.slabs import slab_rows
     p = cfg.params
-    fresh = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap)
+    fresh = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap, p2p=not args.no_p2p)
     fresh.upload_global(F0, U0)
     dev = torch.device("cuda", local)
     tdt = torch.float64 if dtype == PF_F64 else torch.float32
@@ -448,10 +448,13 @@ def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, loc
                 dist.recv(full[f_i][y0:y1], src=r)
         else:
             dist.send(own, dst=0)
+    # the sends read the input fields on NCCL's stream; the solver's streams do not wait for it, and step 2 overwrites those fields
+    torch.cuda.synchronize()
+    dist.barrier()
     for _ in range(steps):
         fresh.step()
     fresh.sync()
-    ok, digests, worst_rel = True, [], 0.0
+    ok, digests, worst_rel, mismatches = True, [], 0.0, []
     if rank == 0:
         with S.Solver(p.nx, p.ny, dtype, device=local) as one:
             q = p.copy()
@@ -481,7 +484,11 @@ def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, loc
                     rel = float(torch.linalg.vector_norm((got - want).double()) / torch.linalg.vector_norm(want.double()).clamp_min(1e-300))
                     worst_rel = max(worst_rel, rel)
                     continue
-                ok = ok and bool(torch.equal(got.view(itype), want.view(itype)))
+                same = bool(torch.equal(got.view(itype), want.view(itype)))
+                if not same:
+                    bad_rows = torch.nonzero((got.view(itype) != want.view(itype)).any(dim=1)).flatten()
+                    mismatches.append({"rank": r, "field": "FU"[f_i], "rows": int(bad_rows.numel()), "first": int(bad_rows[0]) + y0, "last": int(bad_rows[-1]) + y0})
+                ok = ok and same
                 for a, b in ((y0, min(y0 + g, y1)), (max(y1 - g, y0), y1)):
                     hg = hashlib.sha256(got[a - y0:b - y0].cpu().numpy().tobytes()).hexdigest()
                     hw = hashlib.sha256(want[a - y0:b - y0].cpu().numpy().tobytes()).hexdigest()
@@ -489,6 +496,7 @@ def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, loc
                     digests.append(hg[:16])
         else:
             dist.send(own, dst=0)
+    torch.cuda.synchronize()
     fresh.close()
     del full
     torch.cuda.empty_cache()
@@ -503,7 +511,7 @@ def parity_check(args, cfg, dtype, runner, F0, U0, torch, dist, rank, world, loc
     return {"steps": steps, "bit_identical": bool(ok), "ranks": world,
             "what": f"{steps} steps of the {p.nx}x{p.ny} grid on {world} slabs vs the whole grid on rank 0's GPU: all owned rows compared as "
                     f"integers on the device; SHA-256 of the {g} rows at both ends of every slab (first 16 hex digits below)",
-            "sha256_boundary_rows": digests}
+            "sha256_boundary_rows": digests, "mismatches": mismatches}
 
 
 def weak_base(args, dtype, torch, dist, rank, local):
@@ -584,6 +592,7 @@ def main():
                     help="initial state: the config's dendrite seed (default, flat far field), or the smooth / seeded-noise fields of SURVEY 8d")
     ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
     ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
+    ap.add_argument("--no-p2p", action="store_true", help="N > 1: halo rows through NCCL send/recv instead of the device-initiated peer stores")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the 3-step bit comparison against the whole grid on one GPU")
     ap.add_argument("--no-weak-base", action="store_true", help="N > 1: skip timing one rank's slab alone on rank 0")

@@ -254,6 +254,26 @@ PF_API int  pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_
  * The transport (NCCL send/recv or peer copies) is the caller's; rows are contiguous nx*ghost reals. */
 PF_API int  pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, void** recv_ptr, size_t* count);
 
+/* ---- device-initiated halo exchange over NVLink peer memory (one process per GPU of one box) -----------------------
+ * A rank exports its fields and its flag block (cudaIpc), the neighbours map them; after its edge rows are computed a rank
+ * copies them straight into the neighbour's ghost rows and publishes the exchange number `value` into the neighbour's flag
+ * word (pf_halo_push_async: one small kernel, system-scope release); the neighbour's next edge-row launch is preceded by
+ * pf_halo_wait_async (one-thread kernel, acquire). No NCCL call and no host synchronisation per step. The handles are
+ * opaque 64-byte blobs to be carried between the processes by the caller (any transport). */
+enum { PF_IPC_HANDLE_BYTES = 64, PF_HALO_FLAG_FROM_LO = 0, PF_HALO_FLAG_FROM_HI = 1 };
+PF_API int   pf_ipc_export(pf_solver* s, void* dev_ptr, void* handle);             /* dev_ptr: a pf_field_alloc field or pf_halo_flags() */
+PF_API int   pf_ipc_open(pf_solver* s, const void* handle, void** mapped);         /* in ANOTHER process of the box */
+PF_API int   pf_ipc_close(pf_solver* s, void* mapped);
+PF_API void* pf_halo_flags(pf_solver* s);                                           /* this rank's flag block (device memory, zeroed) */
+/* side 0: my first `ghost` owned rows go to the lower neighbour, whose ghost rows start at row `peer_first_row` of its
+ * allocation (its ghost_lo + ny_local); side 1: my last `ghost` owned rows go to the upper neighbour (peer_first_row = 0).
+ * peer_fields[i] / peer_flags are MAPPED pointers of the neighbour's fields / flag block; peer_flag_index says which of its
+ * words to publish into (PF_HALO_FLAG_FROM_HI when I am its upper neighbour, i.e. side 0). */
+PF_API int   pf_halo_push_async(pf_solver* s, int side, int n_fields, const void* const* fields, void* const* peer_fields,
+                                size_t peer_first_row, void* peer_flags, int peer_flag_index, unsigned value, int on_aux_stream);
+PF_API int   pf_halo_wait_async(pf_solver* s, int flag_index, unsigned value, int on_aux_stream);
+PF_API int   pf_halo_check(pf_solver* s);   /* after a synchronisation: PF_ERR_CUDA if a wait gave up (neighbour gone) */
+
 /* ---- semi-implicit solver on slabs: the step in phases --------------------- */
 /* semi_implicit_solver_step_based (simulation.cu:732-926) cut where ranks must talk. The library has no communication
  * code; per time step the caller runs, on every rank in lock step (all calls enqueue on pf_stream and return):
