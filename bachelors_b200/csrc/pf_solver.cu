@@ -17,6 +17,7 @@
 #include "pf_common.cuh"
 #include "pf_fused.cuh"
 #include "pf_stream.cuh"
+#include "pf_euler.cuh"
 #include "pf_general.cuh"
 #include "pf_si_coop.cuh"
 #include "pf_app.cuh"
@@ -567,8 +568,33 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
     return PF_OK;
 }
 
-// One launch = one whole time step (or one Merson attempt). The streaming kernel is the product path; a step with the
-// corrector guess (a different right-hand side, simulation.cu:221-225) takes the tiled kernel.
+// ---- Euler tile kernel (pf_euler.cuh): launch geometry, measured with tools/kbench.cu on B200 at 2048^2 ---------------------------
+// fp64: R = 8 rows per tile, 7 CTAs of 128 threads per SM (72 registers): 26.8 us (R = 8 at 6 or 8 CTAs, R = 6, 10, 12, 16, 96- / 192- /
+// 256-thread tiles: 27.8-31.4); fp32: 8 CTAs: 19.0 us; with anisotropy (atan2f / cosf per cell): R = 4, 6 CTAs: 41.0 us.
+template <typename Real, bool ANISO>
+static int launch_euler_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bit)
+{
+    constexpr int EW = 128, R = ANISO ? 4 : 8, MINB = ANISO ? 6 : (sizeof(Real) == 8 ? 7 : 8);
+    auto kern = k_euler_tile<Real, ANISO, EW, R, MINB>;
+    const size_t smem = euler_tile_smem_bytes<Real, EW, R>();
+    if(!(s->stream_attr_done & (1u << inst_bit)))
+    {
+        PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        s->stream_attr_done |= 1u << inst_bit;
+    }
+    const int own_rows = a.own_y1 - a.own_y0;
+    s->run_used = false;
+    if(own_rows <= 0) return PF_OK;
+    cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
+    dim3 grid((unsigned)((a.nx + (EW - 2 * EULER_HALO) - 1) / (EW - 2 * EULER_HALO)), (unsigned)((own_rows + R - 1) / R));
+    kern<<<grid, EW, smem, stream>>>(a);
+    PF_LAUNCH_CHECK(s);
+    return PF_OK;
+}
+
+// One launch = one whole time step (or one Merson attempt): the Euler tile kernel (pf_euler.cuh) for the one-stage scheme, the
+// streaming kernel (pf_stream.cuh) for RK4 and Merson; a step with the corrector guess (a different right-hand side,
+// simulation.cu:221-225) takes the 2-D tiled kernel of pf_fused.cuh.
 template <typename Real>
 static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
 {
@@ -576,8 +602,8 @@ static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
     const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
     switch(scheme * 2 + (aniso ? 1 : 0))
     {
-        case 0: return launch_stream_inst<Real, SCHEME_EULER, false>(s, a, base);
-        case 1: return launch_stream_inst<Real, SCHEME_EULER, true>(s, a, base);
+        case 0: return launch_euler_inst<Real, false>(s, a, base);
+        case 1: return launch_euler_inst<Real, true>(s, a, base);
         case 2: return launch_stream_inst<Real, SCHEME_RK4, false>(s, a, base);
         case 3: return launch_stream_inst<Real, SCHEME_RK4, true>(s, a, base);
         case 4: return launch_stream_inst<Real, SCHEME_RKM, false>(s, a, base);

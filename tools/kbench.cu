@@ -18,6 +18,7 @@
 #include "../bachelors_b200/csrc/pf_common.cuh"
 #include "../bachelors_b200/csrc/pf_fused.cuh"
 #include "../bachelors_b200/csrc/pf_stream.cuh"
+#include "../bachelors_b200/csrc/pf_euler.cuh"
 
 using namespace pf;
 
@@ -91,6 +92,18 @@ static void launch_stream(FusedArgs<Real> a, int nch)
     a.nch = std::min(nch, a.own_y1 - a.own_y0);
     kern<<<a.strips * a.nch, 32 * WARPS, smem>>>(a);
 }
+
+// the Euler tile kernel (pf_euler.cuh): EW threads, R rows per tile, MINB CTAs per SM; the chunk argument is unused
+template <typename Real, bool ANISO, int EW, int R, int MINB>
+static void launch_euler_tile(FusedArgs<Real> a, int)
+{
+    const size_t smem = euler_tile_smem_bytes<Real, EW, R>();
+    auto kern = k_euler_tile<Real, ANISO, EW, R, MINB>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    dim3 grid((a.nx + (EW - 2 * EULER_HALO) - 1) / (EW - 2 * EULER_HALO), (a.own_y1 - a.own_y0 + R - 1) / R);
+    kern<<<grid, EW, smem>>>(a);
+}
+#define VE(Real, ANISO, EW, R, MB) Variant<Real>{ "euler tile ew" #EW " r" #R " b" #MB, launch_euler_tile<Real, ANISO, EW, R, MB>, 0 }
 
 template <typename Real>
 struct Variant { std::string name; void (*fn)(FusedArgs<Real>, int); int chunk; };
