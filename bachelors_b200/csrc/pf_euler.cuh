@@ -16,7 +16,7 @@
 //
 // Boundaries (reference boundary_sample, simulation.cu:33-85): periodic edges wrap the index at load time; outside a
 // non-periodic edge the ghost value is formed from the edge cell (Neumann: the same value, Dirichlet: 0 - value).
-// Requires Phi_boundary == T_boundary and no corrector guess, like the streaming kernel. Slabs: row0 / rows_local / own_y0..1
+// Slabs: row0 / rows_local / own_y0..1
 // as in FusedArgs; one ghost row per side.
 #pragma once
 #include "pf_common.cuh"
@@ -29,7 +29,12 @@ enum { EULER_HALO = 4 };      // columns of halo on each side of a tile: 1 is ne
 template <typename Real, int EW, int R>
 constexpr size_t euler_tile_smem_bytes() { return sizeof(typename Vec2T<Real>::type) * (size_t) R * EW; }
 
-template <typename Real, bool ANISO, int EW, int R, int MINB>
+// GENERAL = false: the plain step on the lean right-hand side (no corrector guess, no source term).
+// GENERAL = true: the whole parameter space of the reference's Euler path - the corrector-guess form of the RHS (simulation.cu:221-225,
+// run-time flag), the source term fu of do_exact, and the corrector iteration's form y(n+1) = {F, U_base} + dt * f(F, U)
+// (simulation.cu:288-302; a.U_base != NULL) - in the same single launch.
+// Both: Phi and T may have different NON-periodic boundary types (a.bc, a.bc_T); periodic must be both or none.
+template <typename Real, bool ANISO, bool GENERAL, int EW, int R, int MINB>
 __global__ void __launch_bounds__(EW, MINB)
 k_euler_tile(const FusedArgs<Real> a)
 {
@@ -38,7 +43,7 @@ k_euler_tile(const FusedArgs<Real> a)
     V2* const sm = reinterpret_cast<V2*>(pf_smem_raw);
     constexpr int EWI = EW - 2 * EULER_HALO;
 
-    const int nx = a.nx, NY = a.ny_global, bc = a.bc;
+    const int nx = a.nx, NY = a.ny_global, bc = a.bc, bcT = a.bc_T;
     const bool periodic = bc == PF_BOUNDARY_PERIODIC;
     const int tx = (int) threadIdx.x;
     const int gx = (int) blockIdx.x * EWI - EULER_HALO + tx;               // this thread's column (halo threads: beside the tile, maybe outside the grid)
@@ -69,6 +74,12 @@ k_euler_tile(const FusedArgs<Real> a)
     for(int j = 0; j < R + 2; j++) { yF[j] = a.F[off[j]]; yT[j] = a.U[off[j]]; }
 
     // 2. canonical values (the reference's blend "0 + y*1" turns -0 into +0), ghost values outside non-periodic edges, publish
+    Real rawF[GENERAL ? R : 1];                                            // the corrector form adds to the RAW Phi (simulation.cu:299)
+    if(GENERAL)
+    {
+        #pragma unroll
+        for(int j = 0; j < R; j++) rawF[j] = yF[j + 1];
+    }
     #pragma unroll
     for(int j = 0; j < R + 2; j++) { yF[j] = canon_zero(yF[j]); yT[j] = canon_zero(yT[j]); }
     if(!periodic)
@@ -78,14 +89,14 @@ k_euler_tile(const FusedArgs<Real> a)
         for(int j = 0; j < R + 2; j++)
         {
             const int g = gy0 - 1 + j;
-            if(g < 0 || g >= NY) { yF[j] = ghost_of(yF[j], bc); yT[j] = ghost_of(yT[j], bc); }
+            if(g < 0 || g >= NY) { yF[j] = ghost_of(yF[j], bc); yT[j] = ghost_of(yT[j], bcT); }
         }
     }
     #pragma unroll
     for(int j = 0; j < R; j++)
     {
         V2 v; v.x = yF[j + 1]; v.y = yT[j + 1];
-        if(out_x) { v.x = ghost_of(v.x, bc); v.y = ghost_of(v.y, bc); }     // the column beside a non-periodic edge: the edge column mirrored
+        if(out_x) { v.x = ghost_of(v.x, bc); v.y = ghost_of(v.y, bcT); }    // the column beside a non-periodic edge: the edge column mirrored
         sm[j * EW + tx] = v;
     }
     __syncthreads();
@@ -100,8 +111,19 @@ k_euler_tile(const FusedArgs<Real> a)
         {
             const V2 e = sm[j * EW + tx + 1], w = sm[j * EW + tx - 1];
             Real kF, kT;
-            rhs_cell_lean<Real, ANISO>(a.k, yF[j + 1], e.x, w.x, yF[j + 2], yF[j], yT[j + 1], e.y, w.y, yT[j + 2], yT[j], kF, kT);
             const unsigned idx = (unsigned)(g - a.row0) * (unsigned) nx + (unsigned) gx;
+            if(GENERAL)
+            {
+                rhs_cell<Real, ANISO>(a.k, yF[j + 1], e.x, w.x, yF[j + 2], yF[j], yT[j + 1], e.y, w.y, yT[j + 2], yT[j], kF, kT);
+                if(a.U_base)
+                {
+                    a.out_F[idx] = pf_fma(a.k.dt, kF, rawF[j]);             // simulation.cu:299-300
+                    a.out_U[idx] = pf_fma(a.k.dt, kT, a.U_base[idx]);
+                    continue;
+                }
+            }
+            else
+                rhs_cell_lean<Real, ANISO>(a.k, yF[j + 1], e.x, w.x, yF[j + 2], yF[j], yT[j + 1], e.y, w.y, yT[j + 2], yT[j], kF, kT);
             a.out_F[idx] = pf_fma(a.k.dt, kF, yF[j + 1]);                   // simulation.cu:233-234
             a.out_U[idx] = pf_fma(a.k.dt, kT, yT[j + 1]);
         }

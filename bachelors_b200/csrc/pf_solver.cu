@@ -571,11 +571,12 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
 // ---- Euler tile kernel (pf_euler.cuh): launch geometry, measured with tools/kbench.cu on B200 at 2048^2 ---------------------------
 // fp64: R = 8 rows per tile, 7 CTAs of 128 threads per SM (72 registers): 26.8 us (R = 8 at 6 or 8 CTAs, R = 6, 10, 12, 16, 96- / 192- /
 // 256-thread tiles: 27.8-31.4); fp32: 8 CTAs: 19.0 us; with anisotropy (atan2f / cosf per cell): R = 4, 6 CTAs: 41.0 us.
-template <typename Real, bool ANISO>
+// GENERAL: corrector guess / source term / corrector iteration / different boundary types of Phi and T (smaller tiles: more state).
+template <typename Real, bool ANISO, bool GENERAL = false>
 static int launch_euler_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bit)
 {
-    constexpr int EW = 128, R = ANISO ? 4 : 8, MINB = ANISO ? 6 : (sizeof(Real) == 8 ? 7 : 8);
-    auto kern = k_euler_tile<Real, ANISO, EW, R, MINB>;
+    constexpr int EW = 128, R = (ANISO || GENERAL) ? 4 : 8, MINB = (ANISO || GENERAL) ? 6 : (sizeof(Real) == 8 ? 7 : 8);
+    auto kern = k_euler_tile<Real, ANISO, GENERAL, EW, R, MINB>;
     const size_t smem = euler_tile_smem_bytes<Real, EW, R>();
     if(!(s->stream_attr_done & (1u << inst_bit)))
     {
@@ -621,7 +622,7 @@ static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, c
     a.row0 = s->slab.y0 - s->ghost_lo; a.rows_local = s->rows_alloc;
     a.own_y0 = s->slab.y0; a.own_y1 = s->slab.y0 + s->slab.ny_local;
     if(s->win_y1 > s->win_y0) { a.own_y0 = std::max(a.own_y0, s->win_y0); a.own_y1 = std::min(a.own_y1, s->win_y1); }
-    a.bc = p.Phi_boundary;
+    a.bc = p.Phi_boundary; a.bc_T = p.T_boundary; a.U_base = nullptr;
     a.wrap_y = (p.Phi_boundary == PF_BOUNDARY_PERIODIC && !s->slab.has_lo && !s->slab.has_hi) ? 1 : 0;
     a.k = make_consts<Real>(p);
     a.err_bits = s->d_err;
@@ -654,27 +655,43 @@ static int launch_rhs_general(pf_solver* s, const pf_params& p, bool is_euler, i
     return PF_OK;
 }
 
-// explicit_solver_euler_step_based: reference simulation.cu:283-311.
+// The Euler tile kernel serves every parameter combination whose loads can share one geometry: Phi and T both periodic or both not.
+static bool euler_tile_eligible(const pf_solver* s, const pf_params& p)
+{
+    const bool perF = p.Phi_boundary == PF_BOUNDARY_PERIODIC, perT = p.T_boundary == PF_BOUNDARY_PERIODIC;
+    if(perF != perT) return false;
+    if(perF && (s->slab.has_lo != s->slab.has_hi)) return false;
+    if(p.do_exact && !s->is_full_grid()) return false;
+    return true;
+}
+
+// explicit_solver_euler_step_based: reference simulation.cu:283-311. One launch in every case the tile kernel is eligible for:
+// the plain step (lean RHS), and - GENERAL instantiation - the corrector-guess RHS, the source term of do_exact, different
+// non-periodic boundary types for Phi and T, and the corrector iteration y(n+1) = {F, U_base} + dt f(F, U).
 template <typename Real>
 static int euler_step_based(pf_solver* s, const pf_params& p, const Real* F, const Real* U, const Real* U_base, Real* nF, Real* nU, pf_step_info* info)
 {
-    if(U == U_base)
+    if(euler_tile_eligible(s, p))
     {
-        if(fused_eligible(s, p))
-        {
-            FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
-            if(int rc = launch_fused<Real>(s, SCHEME_EULER, p.S != 0, a)) return rc;
-        }
-        else
-        {
-            if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "mixed boundary types are single-GPU only");
-            Real one = 1; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
-            if(int rc = launch_rhs_general<Real>(s, p, true, 1, &one, Fs, Us, nF, nU)) return rc;
-        }
+        FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
+        const bool general = U != U_base || p.do_corrector_guess || p.do_exact || p.Phi_boundary != p.T_boundary;
+        if(U != U_base) a.U_base = U_base;
+        const int bit = 12 + (sizeof(Real) == 8 ? 0 : 2) + (p.S != 0 ? 1 : 0);
+        int rc;
+        if(!general)     rc = launch_fused<Real>(s, SCHEME_EULER, p.S != 0, a);
+        else if(p.S != 0) rc = launch_euler_inst<Real, true, true>(s, a, bit);
+        else              rc = launch_euler_inst<Real, false, true>(s, a, bit);
+        if(rc) return rc;
+    }
+    else if(U == U_base)
+    {
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "periodic mixed with non-periodic boundary types is single-GPU only");
+        Real one = 1; const Real* Fs[1] = {F}; const Real* Us[1] = {U};
+        if(int rc = launch_rhs_general<Real>(s, p, true, 1, &one, Fs, Us, nF, nU)) return rc;
     }
     else
     {
-        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "the corrector loop is single-GPU only");
+        if(!s->is_full_grid()) return fail(s, PF_ERR_UNSUPPORTED, "periodic mixed with non-periodic boundary types is single-GPU only");
         void *dF, *dU;
         if(int rc = get_scratch(s, 0, &dF)) return rc;
         if(int rc = get_scratch(s, 1, &dU)) return rc;

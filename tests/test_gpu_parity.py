@@ -301,6 +301,38 @@ def test_run_is_one_multi_step_launch_with_the_bits_of_single_steps(solver, size
         assert done2 == 3 and np.array_equal(s.download(Fo2), ref2[0]) and np.array_equal(s.download(Uo2), ref2[1])
 
 
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("variant", ["guess_periodic", "neumann_dirichlet", "dirichlet_neumann_aniso_guess", "corrector_loop", "corrector_loop_mixed", "exact_source"])
+def test_euler_parameter_space_is_one_launch_per_rhs(variant, dtype):
+    """The Euler tile kernel (pf_euler.cuh, GENERAL instantiation) serves the reference's whole Euler parameter space - corrector
+    guess (simulation.cu:221-225), different non-periodic boundary types of Phi and T (:186-187), the corrector loop (:928-1008), the
+    source term of do_exact - with ONE launch per right-hand-side evaluation, bit-identical to the CPU oracle."""
+    kw = dict(guess_periodic=dict(do_corrector_guess=1, Phi_boundary="periodic", T_boundary="periodic"),
+              neumann_dirichlet=dict(Phi_boundary="neumann", T_boundary="dirichlet"),
+              dirichlet_neumann_aniso_guess=dict(Phi_boundary="dirichlet", T_boundary="neumann", S=0.3, do_corrector_guess=1),
+              corrector_loop=dict(do_corrector_loop=1, corrector_max_iters=3, do_corrector_guess=1),
+              corrector_loop_mixed=dict(do_corrector_loop=1, corrector_max_iters=2, Phi_boundary="dirichlet", T_boundary="neumann", S=0.2),
+              exact_source=dict(do_exact=1))[variant]
+    nx, ny, steps = 157, 93, 4
+    p = default_params(solver="explicit", nx=nx, ny=ny, L0=nx / 128.0, **kw)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    want = oracle_replay(p, F0, U0, dtype, steps)
+    with S.Solver(nx, ny, dtype) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        l0 = s.kernel_launches
+        q = p.copy()
+        for i in range(steps):
+            q.iter, q.time = i, i * p.dt
+            s.step(q, F, U, nF, nU)
+            F, nF = nF, F; U, nU = nU, U
+        launches = s.kernel_launches - l0
+        gF, gU = s.download(F), s.download(U)
+    iters = p.corrector_max_iters if p.do_corrector_loop else 0
+    assert launches == steps * (1 + iters), launches
+    assert np.array_equal(gF, want[0]) and np.array_equal(gU, want[1])
+
+
 def test_run_stops_at_stop_time():
     nx = ny = 64
     p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=0.5)

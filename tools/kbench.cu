@@ -58,7 +58,7 @@ static FusedArgs<Real> make_args(const pf_params& p, const Real* F, const Real* 
     FusedArgs<Real> a; memset(&a, 0, sizeof a);
     a.F = F; a.U = U; a.out_F = oF; a.out_U = oU;
     a.nx = p.nx; a.ny_global = p.ny; a.row0 = 0; a.rows_local = p.ny; a.own_y0 = 0; a.own_y1 = p.ny;
-    a.bc = p.Phi_boundary; a.wrap_y = p.Phi_boundary == PF_BOUNDARY_PERIODIC;
+    a.bc = p.Phi_boundary; a.bc_T = p.T_boundary; a.U_base = nullptr; a.wrap_y = p.Phi_boundary == PF_BOUNDARY_PERIODIC;
     a.k = make_consts<Real>(p);
     Real dt = (Real) p.dt;
     if(scheme == SCHEME_RK4) { a.w[0] = dt / 2; a.w[1] = dt / 2; a.w[2] = dt; a.w[3] = dt / 6; }
@@ -98,7 +98,7 @@ template <typename Real, bool ANISO, int EW, int R, int MINB>
 static void launch_euler_tile(FusedArgs<Real> a, int)
 {
     const size_t smem = euler_tile_smem_bytes<Real, EW, R>();
-    auto kern = k_euler_tile<Real, ANISO, EW, R, MINB>;
+    auto kern = k_euler_tile<Real, ANISO, false, EW, R, MINB>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     dim3 grid((a.nx + (EW - 2 * EULER_HALO) - 1) / (EW - 2 * EULER_HALO), (a.own_y1 - a.own_y0 + R - 1) / R);
     kern<<<grid, EW, smem>>>(a);
