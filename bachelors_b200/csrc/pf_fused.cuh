@@ -35,8 +35,8 @@ struct FusedArgs {
     int nx, ny_global;
     int row0, rows_local;              // local allocation = global rows [row0, row0 + rows_local)
     int own_y0, own_y1;                // global rows this launch must produce
-    int bc;                            // boundary type of both fields (Euler tile kernel: of Phi)
-    int bc_T;                          // Euler tile kernel (pf_euler.cuh): boundary type of T (both periodic or both not)
+    int bc;                            // boundary type of Phi (tiled kernel of this file: of both fields)
+    int bc_T;                          // streaming and Euler tile kernels: boundary type of T (both periodic or both not)
     const Real* U_base;                // Euler tile kernel, corrector iteration: y(n+1) = {F, U_base} + dt f(F, U); NULL: the plain step
     int wrap_y;                        // single GPU + periodic: wrap rows modulo ny_global
     int strips, nch;                   // streaming kernel (pf_stream.cuh): column strips x row chunks = work units; chunk c produces rows

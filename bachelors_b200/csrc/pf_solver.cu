@@ -631,9 +631,13 @@ static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, c
 
 static bool fused_eligible(const pf_solver* s, const pf_params& p)
 {
-    if(p.Phi_boundary != p.T_boundary) return false;                 // mixed boundary types: general path
+    // the single-kernel paths share one load geometry for both fields: Phi and T both periodic or both not (any Dirichlet / Neumann mix);
+    // the tiled kernel that serves the corrector guess knows one boundary type only
+    const bool perF = p.Phi_boundary == PF_BOUNDARY_PERIODIC, perT = p.T_boundary == PF_BOUNDARY_PERIODIC;
+    if(perF != perT) return false;
+    if(p.Phi_boundary != p.T_boundary && p.do_corrector_guess) return false;
     if(p.do_exact) return false;                                      // nonzero source term fu in every stage: general per-stage path
-    if(p.Phi_boundary == PF_BOUNDARY_PERIODIC && (s->slab.has_lo != s->slab.has_hi)) return false;
+    if(perF && (s->slab.has_lo != s->slab.has_hi)) return false;
     return true;
 }
 

@@ -29,8 +29,8 @@
 // register operand, which only happens in the `CHECKED` form of the loop body: iterations are grouped by U, and a
 // group runs the straight-line form (no activity tests, no boundary selects, one basic block per row) whenever all
 // stages are active and no stage row is a domain edge row. Periodic edges wrap the global index at load time.
-// Requires Phi_boundary == T_boundary and no corrector guess (otherwise the host falls back to the tiled kernel /
-// the general per-stage kernels).
+// Phi and T may have different NON-periodic boundary types (a.bc, a.bc_T); periodic must be both or none, and the corrector
+// guess is not served (otherwise the host falls back to the tiled kernel / the general per-stage kernels).
 //
 // Multi-GPU slabs: `row0` is the global row of local row 0; the launch produces rows [own_y0, own_y1) and reads
 // H rows beyond them, which the slab layout provides as ghost rows.
@@ -107,7 +107,8 @@ template <typename Real>
 __device__ __forceinline__ void stream_store_ghost(const FusedArgs<Real>& a, const StreamCtx<Real>& c, typename Vec2T<Real>::type* p, const Real vF, const Real vT)
 {
     typename Vec2T<Real>::type g; g.x = vF; g.y = vT;
-    if(a.bc == PF_BOUNDARY_DIRICHLET_ZERO) { g.x = (Real) 0 - vF; g.y = (Real) 0 - vT; }      // uniform branch; Neumann repeats the edge cell
+    if(a.bc == PF_BOUNDARY_DIRICHLET_ZERO) g.x = (Real) 0 - vF;                // uniform branches; Neumann repeats the edge cell
+    if(a.bc_T == PF_BOUNDARY_DIRICHLET_ZERO) g.y = (Real) 0 - vT;
     if(c.x_lo_edge) p[-1] = g;
     if(c.x_hi_edge) p[+1] = g;
 }
@@ -157,8 +158,8 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
     }
     if(CHECKED && a.bc != PF_BOUNDARY_PERIODIC)
     {
-        if(row == a.ny_global - 1) { NF = ghost_of(CF, a.bc); NT = ghost_of(CT, a.bc); }
-        if(row == 0)               { SF = ghost_of(CF, a.bc); ST = ghost_of(CT, a.bc); }
+        if(row == a.ny_global - 1) { NF = ghost_of(CF, a.bc); NT = ghost_of(CT, a.bc_T); }
+        if(row == 0)               { SF = ghost_of(CF, a.bc); ST = ghost_of(CT, a.bc_T); }
     }
     Real kF, kT;
     rhs_cell_lean<Real, ANISO>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);       // kT without the reference's "+ fu"

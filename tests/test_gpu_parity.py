@@ -333,6 +333,32 @@ def test_euler_parameter_space_is_one_launch_per_rhs(variant, dtype):
     assert np.array_equal(gF, want[0]) and np.array_equal(gU, want[1])
 
 
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("solver", ["explicit-rk4", "explicit-rk4-adaptive"])
+@pytest.mark.parametrize("bcs", [("neumann", "dirichlet"), ("dirichlet", "neumann")])
+def test_streaming_kernel_takes_different_boundary_types_for_phi_and_t(solver, bcs, dtype):
+    """Independent non-periodic boundary types of Phi and T (simulation.cu:186-187) stay on the one-launch streaming kernel:
+    one launch per step / attempt, bit-identical to the CPU oracle."""
+    nx, ny, steps = 261, 150, 3
+    tol = 1e-7 if dtype == PF_F64 else 1e-4
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=0.2, Phi_boundary=bcs[0], T_boundary=bcs[1], Phi_tolerance=tol, T_tolerance=tol)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+    want = oracle_replay(p, F0, U0, dtype, steps)
+    with S.Solver(nx, ny, dtype) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        l0, attempts, t = s.kernel_launches, 0, 0.0
+        q = p.copy()
+        for i in range(steps):
+            q.iter, q.time = i, t
+            info = s.step(q, F, U, nF, nU)
+            t += info.dt_advanced
+            attempts += info.Phi_iters
+            F, nF = nF, F; U, nU = nU, U
+        assert s.kernel_launches - l0 == attempts
+        assert np.array_equal(s.download(F), want[0]) and np.array_equal(s.download(U), want[1]) and abs(t - want[2]) <= 1e-15
+
+
 def test_run_stops_at_stop_time():
     nx = ny = 64
     p = default_params(solver="explicit-rk4", nx=nx, ny=ny, L0=0.5)
