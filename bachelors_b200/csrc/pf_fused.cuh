@@ -50,6 +50,14 @@ struct FusedArgs {
     // RKM, one launch per attempt (pf_stream.cuh): the last unit to finish hands the two norms and err_seq to the host through
     // mapped pinned memory (err_host[0..2]) and re-arms err_bits / err_ticket; NULL: the words stay on the device for the caller
     unsigned long long* err_host; unsigned* err_ticket; unsigned long long err_seq;
+    // slabs, k_stream_step_halo (pf_stream.cuh): the halo hand-over inside the step kernel. Side 0 = lower neighbour, 1 = upper.
+    // The units of the first / last chunk wait until this rank's flag word `side` has reached halo_e (the neighbour's rows of the
+    // previous exchange have landed in the ghost rows they read), and after their rows are stored copy the slab's first / last
+    // halo_g rows into peer_F/U[side] (mapped peer memory, already offset to the first ghost row to fill); the last of them
+    // publishes halo_e + 1 into peer_flag[side]. A NULL peer_flag[side]: no neighbour on that side.
+    unsigned halo_e; int halo_g;
+    unsigned* halo_flags;
+    Real* peer_F[2]; Real* peer_U[2]; unsigned* peer_flag[2];
 };
 
 template <int SCHEME> struct SchemeStages { static constexpr int value = SCHEME == SCHEME_EULER ? 1 : (SCHEME == SCHEME_RK4 ? 4 : 5); };

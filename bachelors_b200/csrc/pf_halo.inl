@@ -83,6 +83,33 @@ int pf_halo_wait_async(pf_solver* s, int flag_index, unsigned value, int on_aux_
     return PF_OK;
 }
 
+int pf_halo_link(pf_solver* s, int n_fields, void* const* fields, void* const* lo_fields, size_t lo_first_row, void* lo_flags,
+                 void* const* hi_fields, void* hi_flags)
+{
+    if(int rc = bind(s)) return rc;
+    s->halo.on = false;
+    if(n_fields == 0) return PF_OK;                                        // unlink
+    if(n_fields < 2 || n_fields > 8 || !fields) return fail(s, PF_ERR_INVALID, "pf_halo_link: bad field list");
+    if((lo_flags != nullptr) != (s->slab.has_lo != 0) || (hi_flags != nullptr) != (s->slab.has_hi != 0))
+        return fail(s, PF_ERR_INVALID, "pf_halo_link: a neighbour must be linked exactly where the slab has one");
+    if((lo_flags && !lo_fields) || (hi_flags && !hi_fields)) return fail(s, PF_ERR_INVALID, "pf_halo_link: NULL peer field list");
+    if(!pf_halo_flags(s)) return fail(s, PF_ERR_OOM, "pf_halo_link: no flag block");
+    if(((size_t) s->slab.ghost * (size_t) s->nx * s->real_size()) % 16) return fail(s, PF_ERR_UNSUPPORTED, "pf_halo_link: ghost rows are not a multiple of 16 bytes");
+    s->halo.n_fields = n_fields;
+    for(int i = 0; i < n_fields; i++)
+    {
+        s->halo.local[i] = fields[i];
+        s->halo.peer[0][i] = lo_flags ? lo_fields[i] : nullptr;
+        s->halo.peer[1][i] = hi_flags ? hi_fields[i] : nullptr;
+    }
+    s->halo.first_row[0] = lo_first_row; s->halo.first_row[1] = 0;
+    s->halo.peer_flags[0] = (unsigned*) lo_flags; s->halo.peer_flags[1] = (unsigned*) hi_flags;
+    s->halo.e = 0;
+    PF_CUDA(s, cudaMemset(s->halo_flags, 0, HALO_FLAG_WORDS * sizeof(unsigned)));
+    s->halo.on = true;
+    return PF_OK;
+}
+
 int pf_halo_check(pf_solver* s)
 {
     if(int rc = bind(s)) return rc;

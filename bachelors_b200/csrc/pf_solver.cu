@@ -58,6 +58,8 @@ struct pf_solver {
 
     unsigned smem_attr_done = 0;            // bit per fused-kernel instance
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
+    unsigned halo_attr_done = 0;            // same for k_stream_step_halo
+    bool halo_in_kernel = false;            // the last fused launch did the halo hand-over itself
     int stream_resident[16];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
     unsigned* run_progress = nullptr;       // multi-step launches: steps finished by each unit (+ 1 flag word), see StreamRun
     int run_progress_units = 0;
@@ -70,6 +72,7 @@ struct pf_solver {
     bool plain_grid_sync = false;           // PF_OPT_SI_GRID_SYNC: cooperative grid.sync() + partial arrays instead of the flagged sums
     bool force_per_kernel_cg = false;       // PF_OPT_SI_PER_KERNEL: take the per-kernel CG path
     int host_bands = 8;                     // PF_OPT_HOST_BANDS: row bands of the pipelined pf_step_host
+    bool halo_in_kernel_ok = true;          // PF_OPT_HALO_IN_KERNEL: linked slabs hand their rows over inside the RK4 step kernel
     bool rkm_keep_errors = false;           // rows variant: do not zero the error words inside the attempt
     bool rkm_fused = true;                  // path chosen by rkm_begin for the current adaptive step
     bool rkm_handover = false;              // rk4_adaptive_step: the attempt kernel mails its norms to the host (see FusedArgs::err_host)
@@ -88,6 +91,14 @@ struct pf_solver {
     // pf_si_*: the semi-implicit step in phases (slabs); what pf_si_begin_async was given
     struct SiCtx { pf_params p; const void *F = nullptr, *U = nullptr, *U_base = nullptr; void *nF = nullptr, *nU = nullptr; bool active = false; } si;
     unsigned* halo_flags = nullptr;         // device-initiated halo exchange (pf_halo.cuh): words the neighbours write through peer mappings
+    struct HaloLink {                       // pf_halo_link: the neighbours' mapped fields and flag blocks; every whole-slab step exchanges through them
+        bool on = false;
+        int n_fields = 0;
+        void* local[8] = {}; void* peer[2][8] = {};
+        size_t first_row[2] = {0, 0};
+        unsigned* peer_flags[2] = {nullptr, nullptr};
+        unsigned e = 0;                     // exchanges completed so far
+    } halo;
     int64_t launches = 0;
     std::string err;
 
@@ -98,6 +109,7 @@ struct pf_solver {
 };
 
 static thread_local std::string g_create_error;
+static int halo_wait_both(pf_solver* s);
 
 static int fail(pf_solver* s, int code, const char* fmt, ...)
 {
@@ -272,6 +284,7 @@ int pf_set_option(pf_solver* s, int option, int value)
         case PF_OPT_HOST_BANDS:    if(value < 1) return fail(s, PF_ERR_INVALID, "PF_OPT_HOST_BANDS: %d", value); s->host_bands = value; return PF_OK;
         case PF_OPT_SI_PER_KERNEL: s->force_per_kernel_cg = value != 0; return PF_OK;
         case PF_OPT_SI_GRID_SYNC:  s->plain_grid_sync = value != 0; return PF_OK;
+        case PF_OPT_HALO_IN_KERNEL: s->halo_in_kernel_ok = value != 0; return PF_OK;
         default: return fail(s, PF_ERR_INVALID, "pf_set_option: unknown option %d", option);
     }
 }
@@ -563,6 +576,25 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
             return PF_OK;
         }
     }
+    if constexpr (HAS_RUN)
+    {
+        // a linked slab (pf_halo_link), whole-slab launch: the halo hand-over happens inside the kernel
+        if(a.halo_flags && s->halo_in_kernel_ok && own_rows / a.nch >= a.halo_g)
+        {
+            auto kern_halo = k_stream_step_halo<Real, SCHEME, ANISO, W, MINB>;
+            if(!(s->halo_attr_done & (1u << inst_bit)))
+            {
+                PF_CUDA(s, cudaFuncSetAttribute(kern_halo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+                PF_CUDA(s, cudaFuncSetAttribute(kern_halo, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+                s->halo_attr_done |= 1u << inst_bit;
+            }
+            kern_halo<<<(unsigned) units, 32 * W, smem, stream>>>(a);
+            PF_LAUNCH_CHECK(s);
+            s->halo_in_kernel = true;
+            return PF_OK;
+        }
+    }
+    if(a.halo_flags) if(int rc = halo_wait_both(s)) return rc;           // linked slab, no in-kernel hand-over: the caller pushes afterwards
     kern<<<(unsigned) units, 32 * W, smem, stream>>>(a);
     PF_LAUNCH_CHECK(s);
     return PF_OK;
@@ -588,6 +620,7 @@ static int launch_euler_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bi
     if(own_rows <= 0) return PF_OK;
     cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
     dim3 grid((unsigned)((a.nx + (EW - 2 * EULER_HALO) - 1) / (EW - 2 * EULER_HALO)), (unsigned)((own_rows + R - 1) / R));
+    if(a.halo_flags) if(int rc = halo_wait_both(s)) return rc;           // linked slab: the caller pushes afterwards
     kern<<<grid, EW, smem, stream>>>(a);
     PF_LAUNCH_CHECK(s);
     return PF_OK;
@@ -627,6 +660,56 @@ static FusedArgs<Real> make_fused_args(const pf_solver* s, const pf_params& p, c
     a.k = make_consts<Real>(p);
     a.err_bits = s->d_err;
     return a;
+}
+
+// ---- linked slabs (pf_halo_link): every whole-slab step of the fixed-step explicit solvers exchanges its edge rows ------------------
+static bool halo_active(const pf_solver* s) { return s->halo.on && s->win_y1 <= s->win_y0 && !s->launch_stream; }
+
+static int halo_index(const pf_solver* s, const void* field)
+{
+    for(int i = 0; i < s->halo.n_fields; i++) if(s->halo.local[i] == field) return i;
+    return -1;
+}
+
+// Fills the in-kernel hand-over of FusedArgs for the output fields nF / nU; false if they are not linked fields.
+template <typename Real>
+static bool halo_fill(pf_solver* s, FusedArgs<Real>& a, void* nF, void* nU)
+{
+    const int iF = halo_index(s, nF), iU = halo_index(s, nU);
+    if(iF < 0 || iU < 0) return false;
+    a.halo_e = s->halo.e; a.halo_g = s->slab.ghost; a.halo_flags = s->halo_flags;
+    for(int side = 0; side < 2; side++)
+    {
+        const bool there = s->halo.peer_flags[side] != nullptr;
+        const size_t off = s->halo.first_row[side] * (size_t) s->nx;
+        a.peer_F[side] = there ? (Real*) s->halo.peer[side][iF] + off : nullptr;
+        a.peer_U[side] = there ? (Real*) s->halo.peer[side][iU] + off : nullptr;
+        a.peer_flag[side] = there ? s->halo.peer_flags[side] + (side == 0 ? HALO_FLAG_FROM_HI : HALO_FLAG_FROM_LO) : nullptr;
+    }
+    return true;
+}
+
+// The same exchange with separate launches around a step kernel that cannot do it itself (Euler tile kernel, chunks shorter than the
+// ghost depth): wait kernels before ...
+static int halo_wait_both(pf_solver* s)
+{
+    for(int side = 0; side < 2; side++)
+        if(s->halo.peer_flags[side]) if(int rc = pf_halo_wait_async(s, side, s->halo.e, 0)) return rc;
+    return PF_OK;
+}
+// ... and push kernels after.
+static int halo_push_both(pf_solver* s, void* nF, void* nU)
+{
+    const int iF = halo_index(s, nF), iU = halo_index(s, nU);
+    for(int side = 0; side < 2; side++)
+    {
+        if(!s->halo.peer_flags[side]) continue;
+        const void* mine[2] = {nF, nU};
+        void* theirs[2] = {s->halo.peer[side][iF], s->halo.peer[side][iU]};
+        if(int rc = pf_halo_push_async(s, side, 2, mine, theirs, s->halo.first_row[side], s->halo.peer_flags[side],
+                                       side == 0 ? HALO_FLAG_FROM_HI : HALO_FLAG_FROM_LO, s->halo.e + 1, 0)) return rc;
+    }
+    return PF_OK;
 }
 
 static bool fused_eligible(const pf_solver* s, const pf_params& p)
@@ -681,11 +764,17 @@ static int euler_step_based(pf_solver* s, const pf_params& p, const Real* F, con
         const bool general = U != U_base || p.do_corrector_guess || p.do_exact || p.Phi_boundary != p.T_boundary;
         if(U != U_base) a.U_base = U_base;
         const int bit = 12 + (sizeof(Real) == 8 ? 0 : 2) + (p.S != 0 ? 1 : 0);
+        const bool hx = U == U_base && halo_active(s) && halo_fill<Real>(s, a, nF, nU);
         int rc;
         if(!general)     rc = launch_fused<Real>(s, SCHEME_EULER, p.S != 0, a);
         else if(p.S != 0) rc = launch_euler_inst<Real, true, true>(s, a, bit);
         else              rc = launch_euler_inst<Real, false, true>(s, a, bit);
         if(rc) return rc;
+        if(hx)
+        {
+            if(int rc2 = halo_push_both(s, nF, nU)) return rc2;
+            s->halo.e++;
+        }
     }
     else if(U == U_base)
     {
@@ -718,7 +807,14 @@ static int rk4_step(pf_solver* s, const pf_params& p, const Real* F, const Real*
     {
         FusedArgs<Real> a = make_fused_args<Real>(s, p, F, U, nF, nU);
         a.w[0] = dt / 2; a.w[1] = dt / 2; a.w[2] = dt; a.w[3] = dt / 6;
+        const bool hx = halo_active(s) && halo_fill<Real>(s, a, nF, nU);
+        s->halo_in_kernel = false;
         if(int rc = launch_fused<Real>(s, SCHEME_RK4, p.S != 0, a)) return rc;
+        if(hx)
+        {
+            if(!s->halo_in_kernel) if(int rc = halo_push_both(s, nF, nU)) return rc;
+            s->halo.e++;
+        }
     }
     else
     {

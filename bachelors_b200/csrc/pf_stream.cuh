@@ -520,6 +520,82 @@ k_stream_step(const FusedArgs<Real> a)
     stream_unit<Real, SCHEME, ANISO, WARPS, false>(a, a.F, a.U, a.out_F, a.out_U, reinterpret_cast<V2*>(pf_smem_raw), strip, chunk);
 }
 
+// One time step of a slab with the halo hand-over to the neighbouring GPUs inside the kernel (see FusedArgs::halo_* and
+// pf_halo.cuh): no separate wait / push launches, so a step is ONE launch and the hand-over of the lower rows - produced in
+// the first iterations of the first chunk - overlaps the rest of the step. Requires chunks of at least halo_g rows.
+// The two cold parts are separate functions (not inlined) so that they do not take part in the register allocation and
+// scheduling of the march.
+__device__ __noinline__ void stream_halo_wait(unsigned* flags, const unsigned e, const unsigned sides)
+{
+    if(threadIdx.x < 2 && (sides >> threadIdx.x & 1u))
+    {
+        unsigned v, spins = 0;
+        for(;;)
+        {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+            if((int)(v - e) >= 0) break;
+            __nanosleep(100);
+            if(++spins > (1u << 24)) { flags[2] = 1u + threadIdx.x; break; }   // HALO_FLAG_STALLED: the neighbour is gone
+        }
+    }
+    __syncthreads();
+}
+
+template <typename Real>
+__device__ __noinline__ void stream_halo_forward(const Real* out_F, const Real* out_U, Real* peer_F, Real* peer_U, const unsigned src0, const unsigned nx,
+                                                 const int rows, const bool own, const unsigned gx, unsigned* ticket, const unsigned strips,
+                                                 unsigned* peer_flag, const unsigned value)
+{
+    if(own)
+        for(int r = 0; r < rows; r++)
+        {
+            peer_F[(unsigned) r * nx + gx] = __ldcg(out_F + src0 + (unsigned) r * nx + gx);
+            peer_U[(unsigned) r * nx + gx] = __ldcg(out_U + src0 + (unsigned) r * nx + gx);
+        }
+    __syncthreads();
+    if(threadIdx.x == 0)
+    {
+        __threadfence_system();                                             // this unit's peer stores before its ticket
+        if(atomicAdd(ticket, 1u) == strips - 1u)
+        {
+            *ticket = 0;
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(peer_flag), "r"(value) : "memory");
+        }
+    }
+}
+
+template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+__global__ void __launch_bounds__(32 * WARPS, MINB)
+k_stream_step_halo(const FusedArgs<Real> a)
+{
+    using V2 = typename Vec2T<Real>::type;
+    extern __shared__ __align__(16) unsigned char pf_smem_raw[];
+    constexpr int H = SchemeStages<SCHEME>::value, EW = 32 * WARPS, EWI = EW - 2 * H;
+    int strip, chunk;
+    stream_unit_to_tile(a, a.bc == PF_BOUNDARY_PERIODIC, (int) blockIdx.x, strip, chunk);
+    {
+        const unsigned sides = (chunk == 0 && a.peer_flag[0] ? 1u : 0u) | (chunk == a.nch - 1 && a.peer_flag[1] ? 2u : 0u);
+        if(sides) stream_halo_wait(a.halo_flags, a.halo_e, sides);
+    }
+    stream_unit<Real, SCHEME, ANISO, WARPS, false>(a, a.F, a.U, a.out_F, a.out_U, reinterpret_cast<V2*>(pf_smem_raw), strip, chunk);
+    {
+        // the columns this strip stored (thread = column, as in stream_unit): every thread forwards what it wrote itself
+        const bool periodic = a.bc == PF_BOUNDARY_PERIODIC;
+        int strip2, chunk2;
+        stream_unit_to_tile(a, periodic, (int) blockIdx.x, strip2, chunk2);
+        const int gx0 = strip2 * EWI - (periodic ? H : 0), cx = (int) threadIdx.x, gx = gx0 + cx;
+        const int cx_lo = (!periodic && gx0 == 0) ? 0 : H, cx_hi = (!periodic && gx0 + EW >= a.nx) ? EW : EW - H;
+        const bool own = cx >= cx_lo && cx < cx_hi && gx < a.nx;
+        if(chunk2 == 0 && a.peer_flag[0])
+            stream_halo_forward<Real>(a.out_F, a.out_U, a.peer_F[0], a.peer_U[0], (unsigned)(a.own_y0 - a.row0) * (unsigned) a.nx, (unsigned) a.nx,
+                                      a.halo_g, own, (unsigned) gx, a.halo_flags + 3, (unsigned) a.strips, a.peer_flag[0], a.halo_e + 1u);
+        if(chunk2 == a.nch - 1 && a.peer_flag[1])
+            stream_halo_forward<Real>(a.out_F, a.out_U, a.peer_F[1], a.peer_U[1], (unsigned)(a.own_y1 - a.halo_g - a.row0) * (unsigned) a.nx, (unsigned) a.nx,
+                                      a.halo_g, own, (unsigned) gx, a.halo_flags + 4, (unsigned) a.strips, a.peer_flag[1], a.halo_e + 1u);
+    }
+}
+
 // r.n_steps time steps per launch (cooperative launch: all units co-resident).
 template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB)

@@ -75,7 +75,7 @@ class _DevArray:
 class SlabRunner:
     """One rank's slab of a global nx x ny grid; steps in lock step with the other ranks of `group`."""
 
-    def __init__(self, params, dtype=PF_F64, rank=None, world=None, device=None, group=None, overlap=True, p2p=True):
+    def __init__(self, params, dtype=PF_F64, rank=None, world=None, device=None, group=None, overlap=True, p2p=True, halo_in_kernel=None):
         self.rank = dist.get_rank(group) if rank is None else rank
         self.world = dist.get_world_size(group) if world is None else world
         self.group = group
@@ -89,6 +89,8 @@ class SlabRunner:
         self.layout = slab_layout(params.ny, self.world, self.rank, self.ghost, self.periodic)
         self.lo, self.hi = neighbours(self.world, self.rank, self.periodic)
         self.solver = S.Solver(params.nx, params.ny, dtype, device=self.device, slab=self.layout)
+        if halo_in_kernel is not None:
+            self.solver.set_option(3, int(halo_in_kernel))          # PF_OPT_HALO_IN_KERNEL
         s = self.solver
         tdt = torch.float64 if dtype == PF_F64 else torch.float32
         dev = torch.device("cuda", self.device)
@@ -122,9 +124,7 @@ class SlabRunner:
         self.window_mid = (y0 + (g if self.layout.has_lo else 0), y1 - (g if self.layout.has_hi else 0))
         self.ev_edge = torch.cuda.Event()
         self.ev_edge.record(self.aux)
-        self.xchg = 0                                   # halo pushes completed per side so far
         self.p2p = bool(p2p and overlap and self.world > 1 and params.solver in (SOLVER_TYPE_EXPLICIT_EULER, SOLVER_TYPE_EXPLICIT_RK4))
-        self._peers = {}
         if self.p2p:
             self._p2p_setup()
 
@@ -156,39 +156,25 @@ class SlabRunner:
                              "ghost_lo": everyone[r]["ghost_lo"], "ny_local": everyone[r]["ny_local"]}
             return opened[r]
 
-        if self.lo is not None:          # my first rows -> the lower neighbour's UPPER ghost rows; I am its upper neighbour
-            q = open_peer(self.lo)
-            self._peers[0] = dict(q, first_row=q["ghost_lo"] + q["ny_local"], flag=1)
-        if self.hi is not None:          # my last rows -> the upper neighbour's LOWER ghost rows (row 0 of its allocation)
-            q = open_peer(self.hi)
-            self._peers[1] = dict(q, first_row=0, flag=0)
+        lo = open_peer(self.lo) if self.lo is not None else None     # my first rows -> its UPPER ghost rows (row ghost_lo + ny_local of its allocation)
+        hi = open_peer(self.hi) if self.hi is not None else None     # my last rows -> its LOWER ghost rows (row 0)
+        n = len(self._field_ptrs)
+        arr = lambda v: (C.c_void_p * n)(*v)
+        s._ck(L.pf_halo_link(s._h, n, arr(self._field_ptrs), arr(lo["fields"]) if lo else None, (lo["ghost_lo"] + lo["ny_local"]) if lo else 0,
+                             lo["flags"] if lo else None, arr(hi["fields"]) if hi else None, hi["flags"] if hi else None))
         self._opened = opened
         dist.barrier(group=self.group)
 
-    def _push(self, side, outF, outU, value):
-        L, s, q = S.lib(), self.solver, self._peers[side]
-        mine = (C.c_void_p * 2)(outF, outU)
-        theirs = (C.c_void_p * 2)(q["fields"][self._ptr_index[outF]], q["fields"][self._ptr_index[outU]])
-        s._ck(L.pf_halo_push_async(s._h, side, 2, mine, theirs, q["first_row"], q["flags"], q["flag"], value, 0))
-
     def _step_p2p(self, p, F, U, nF, nU):
-        """One kernel for the whole slab, then the edge rows go to the neighbours from the device. Everything is in the order of
-        the solver's main stream; nothing waits on the host or on NCCL.
-        The slab is NOT cut into edge and interior launches here: the step kernel is one wave of long-lived CTAs, and an edge
-        launch that takes some of its slots for its first 20 us delays the CTAs that could not start by as much - the whole step
-        ends that much later (measured at 2 GPUs: 518 us against 474 us for the slab alone, with NCCL and with peer stores
-        alike). Serialising the 1 MiB hand-over behind the kernel costs a few us instead."""
+        """ONE call, and for explicit-rk4 ONE kernel: the linked solver (pf_halo_link) waits for the neighbours' rows and hands its own
+        edge rows over from inside the step kernel. Nothing here waits on the host or on NCCL.
+        The slab is NOT cut into edge and interior launches: the step kernel is one wave of long-lived CTAs, and an edge launch that
+        takes some of its slots for its first 20 us delays the CTAs that could not start by as much - the whole step ends that much
+        later (measured at 2 GPUs: 518 us against 474 us for the slab alone, with NCCL and with peer stores alike)."""
         L, s = S.lib(), self.solver
         self.main.wait_event(self.ev_halo)
-        for side in (0, 1):
-            if side in self._peers:
-                s._ck(L.pf_halo_wait_async(s._h, side, self.xchg, 0))       # flag word `side` = "from lo" / "from hi"
         s._ck(L.pf_step_async(s._h, C.byref(p), F, U, nF, nU))
-        for side in (0, 1):
-            if side in self._peers:
-                self._push(side, nF, nU, self.xchg + 1)
         self.ev_main.record(self.main)
-        self.xchg += 1
 
     # -- data movement -----------------------------------------------------------------------------------------
     def owned(self, t):
@@ -363,5 +349,6 @@ class SlabRunner:
             for q in self._opened.values():
                 for m in q["fields"] + [q["flags"]]:
                     L.pf_ipc_close(s._h, m)
-            self._opened, self._peers, self.p2p = {}, {}, False
+            L.pf_halo_link(s._h, 0, None, None, 0, None, None, None)
+            self._opened, self.p2p = {}, False
         self.solver.close()

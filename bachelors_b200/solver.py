@@ -26,7 +26,7 @@ EXPORTS = [
     "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
     "pf_si_begin_async", "pf_si_partials", "pf_si_cg_begin_async", "pf_si_cg_spmv_async", "pf_si_cg_update_async",
     "pf_si_cg_pupdate_async", "pf_si_direction", "pf_si_cg_poll",
-    "pf_ipc_export", "pf_ipc_open", "pf_ipc_close", "pf_halo_flags", "pf_halo_push_async", "pf_halo_wait_async", "pf_halo_check",
+    "pf_ipc_export", "pf_ipc_open", "pf_ipc_close", "pf_halo_flags", "pf_halo_push_async", "pf_halo_wait_async", "pf_halo_check", "pf_halo_link",
 ]
 
 
@@ -94,6 +94,7 @@ def lib():
         "pf_halo_flags": (vp, [vp]),
         "pf_halo_push_async": (i32, [vp, i32, i32, P(vp), P(vp), sz, vp, i32, C.c_uint, i32]),
         "pf_halo_wait_async": (i32, [vp, i32, C.c_uint, i32]), "pf_halo_check": (i32, [vp]),
+        "pf_halo_link": (i32, [vp, i32, P(vp), P(vp), sz, vp, P(vp), vp]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)

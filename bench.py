@@ -332,7 +332,8 @@ def run_cuda_arm(args):
         F0, U0 = np.ascontiguousarray(gF[y0:y1]), np.ascontiguousarray(gU[y0:y1])
         desc += f", field = {args.field}"
 
-    runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap, p2p=not args.no_p2p)
+    runner = SlabRunner(p, dtype, rank=rank, world=world, device=local, overlap=not args.no_overlap, p2p=not args.no_p2p,
+                        halo_in_kernel=None if args.halo_in_kernel < 0 else bool(args.halo_in_kernel))
     runner.upload_global(F0, U0)
     launches0 = runner.solver.kernel_launches
     for _ in range(args.warmup):
@@ -593,6 +594,7 @@ def main():
     ap.add_argument("--wide", action="store_true", help="N = 1 on the 16384 x 2048 slab of the multi-GPU family (weak-scaling base)")
     ap.add_argument("--no-overlap", action="store_true", help="exchange halos only after the interior finished")
     ap.add_argument("--no-p2p", action="store_true", help="N > 1: halo rows through NCCL send/recv instead of the device-initiated peer stores")
+    ap.add_argument("--halo-in-kernel", type=int, default=-1, help="N > 1, explicit-rk4: 1 / 0 = halo hand-over inside / around the step kernel (default: the library's)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the 3-step bit comparison against the whole grid on one GPU")
     ap.add_argument("--no-weak-base", action="store_true", help="N > 1: skip timing one rank's slab alone on rank 0")

@@ -150,6 +150,7 @@ typedef enum pf_option {
     PF_OPT_HOST_BANDS    = 0,  /* row bands of the pipelined pf_step_host (default 8, at most 32) */
     PF_OPT_SI_PER_KERNEL = 1,  /* != 0: semi-implicit step through the per-kernel CG path instead of the one cooperative launch */
     PF_OPT_SI_GRID_SYNC  = 2,  /* != 0: cooperative step with grid.sync() + partial arrays instead of the flagged all-block sums */
+    PF_OPT_HALO_IN_KERNEL = 3, /* linked slabs (pf_halo_link), explicit-rk4: 1 = hand-over inside the step kernel, 0 = wait / push launches around it */
 } pf_option;
 PF_API int  pf_set_option(pf_solver* s, int option, int value);
 
@@ -272,6 +273,15 @@ PF_API void* pf_halo_flags(pf_solver* s);                                       
 PF_API int   pf_halo_push_async(pf_solver* s, int side, int n_fields, const void* const* fields, void* const* peer_fields,
                                 size_t peer_first_row, void* peer_flags, int peer_flag_index, unsigned value, int on_aux_stream);
 PF_API int   pf_halo_wait_async(pf_solver* s, int flag_index, unsigned value, int on_aux_stream);
+/* Links a slab to its neighbours for good: `fields` are this rank's n_fields fields (any of which may be the input or output of a step),
+ * lo_fields / hi_fields the neighbours' SAME fields in the same order (mapped), lo_flags / hi_flags their flag blocks (NULL where the slab
+ * has no neighbour), lo_first_row the row of the lower neighbour's allocation where its upper ghost rows start. From then on every
+ * whole-slab pf_step_async of explicit / explicit-rk4 does the exchange itself: explicit-rk4 INSIDE its one step kernel
+ * (k_stream_step_halo: the first / last chunk's units acquire the neighbours' flags before they start and forward their finished rows),
+ * explicit with a wait launch before and a push launch after its kernel. Collective: every rank of the job links, then a barrier, before
+ * the first step; ghost rows of the first step's inputs must be current. n_fields = 0 unlinks. */
+PF_API int   pf_halo_link(pf_solver* s, int n_fields, void* const* fields, void* const* lo_fields, size_t lo_first_row, void* lo_flags,
+                          void* const* hi_fields, void* hi_flags);
 PF_API int   pf_halo_check(pf_solver* s);   /* after a synchronisation: PF_ERR_CUDA if a wait gave up (neighbour gone) */
 
 /* ---- semi-implicit solver on slabs: the step in phases --------------------- */
