@@ -576,7 +576,7 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
             return PF_OK;
         }
     }
-    if constexpr (HAS_RUN)
+    if constexpr (SCHEME != SCHEME_EULER)
     {
         // a linked slab (pf_halo_link), whole-slab launch: the halo hand-over happens inside the kernel
         if(a.halo_flags && s->halo_in_kernel_ok && own_rows / a.nch >= a.halo_g)
@@ -897,7 +897,16 @@ static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Rea
         }
         a.w[0] = tau / 3; a.w[1] = tau / 6; a.w[2] = tau / 8; a.w[3] = tau * 3 / 8;
         a.w[4] = tau / 2; a.w[5] = -tau * 3 / 2; a.w[6] = tau * 2; a.w[7] = tau / 6;
-        return launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a);
+        // linked slab: every attempt hands its candidate rows to the neighbours (a rejected attempt's rows are overwritten by the next one's)
+        const bool hx = halo_active(s) && halo_fill<Real>(s, a, nF, nU);
+        s->halo_in_kernel = false;
+        if(int rc = launch_fused<Real>(s, SCHEME_RKM, p.S != 0, a)) return rc;
+        if(hx)
+        {
+            if(!s->halo_in_kernel) if(int rc = halo_push_both(s, nF, nU)) return rc;
+            s->halo.e++;
+        }
+        return PF_OK;
     }
     Real* k[10];
     for(int i = 0; i < 10; i++) k[i] = (Real*) s->scratch[i];

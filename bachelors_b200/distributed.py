@@ -124,7 +124,7 @@ class SlabRunner:
         self.window_mid = (y0 + (g if self.layout.has_lo else 0), y1 - (g if self.layout.has_hi else 0))
         self.ev_edge = torch.cuda.Event()
         self.ev_edge.record(self.aux)
-        self.p2p = bool(p2p and overlap and self.world > 1 and params.solver in (SOLVER_TYPE_EXPLICIT_EULER, SOLVER_TYPE_EXPLICIT_RK4))
+        self.p2p = bool(p2p and overlap and self.world > 1 and params.solver in (SOLVER_TYPE_EXPLICIT_EULER, SOLVER_TYPE_EXPLICIT_RK4, SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE))
         if self.p2p:
             self._p2p_setup()
 
@@ -231,7 +231,7 @@ class SlabRunner:
         p.time, p.iter = self.time, self.iter
         L, s = S.lib(), self.solver
         F, U, nF, nU = self._ptrs()
-        if self.p2p:
+        if self.p2p and p.solver != SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE:
             self._step_p2p(p, F, U, nF, nU)
             dt = p.dt
             self.last_attempts = 1
@@ -272,13 +272,20 @@ class SlabRunner:
         max_iters = max(p.T_max_iters, p.Phi_max_iters, 1)
         attempts = 0
         for _ in range(max_iters):
-            # zero the error words before either stream's kernels can touch them
-            self.aux.wait_event(self.ev_main)
-            s._ck(L.pf_rkm_clear_errors_async(s._h, 1))
-            self.ev_aux.record(self.aux)
             t = tau
-            self._launch(lambda a, b: s._ck(L.pf_rkm_attempt_rows_async(s._h, C.byref(p), t, F, U, nF, nU, a, b, 1)),
-                         lambda a, b: s._ck(L.pf_rkm_attempt_rows_async(s._h, C.byref(p), t, F, U, nF, nU, a, b, 0)))
+            if self.p2p:
+                # linked slab: ONE attempt kernel for the whole slab, which also hands the candidate rows to the neighbours
+                self.main.wait_event(self.ev_halo)
+                s._ck(L.pf_rkm_attempt_async(s._h, C.byref(p), t, F, U, nF, nU))
+                self.ev_main.record(self.main)
+                self.ev_aux.record(self.aux)
+            else:
+                # zero the error words before either stream's kernels can touch them
+                self.aux.wait_event(self.ev_main)
+                s._ck(L.pf_rkm_clear_errors_async(s._h, 1))
+                self.ev_aux.record(self.aux)
+                self._launch(lambda a, b: s._ck(L.pf_rkm_attempt_rows_async(s._h, C.byref(p), t, F, U, nF, nU, a, b, 1)),
+                             lambda a, b: s._ck(L.pf_rkm_attempt_rows_async(s._h, C.byref(p), t, F, U, nF, nU, a, b, 0)))
             with torch.cuda.stream(self.comm):
                 self.comm.wait_event(self.ev_main)
                 self.comm.wait_event(self.ev_aux)
