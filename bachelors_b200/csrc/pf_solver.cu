@@ -1448,9 +1448,8 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
             PF_CUDA(s, cudaEventCreateWithFlags(&s->ev_done[i], cudaEventDisableTiming));
         }
     }
-    // bands of >= 64 rows, at most HOST_BANDS_MAX. Measured on B200 / PCIe 5 at 2048^2 fp64 (2 x 32 MiB each way): 1 band 2.50 ms,
-    // 4: 2.06, 8: 1.94, 16: 2.16, 32: 2.55 per call - more bands shorten the pipeline fill but every copy and launch costs
-    // host enqueue time; the two copy directions alone need 1.4 ms when overlapped.
+    // bands of >= 64 rows, at most HOST_BANDS_MAX: more bands shorten the pipeline fill and drain but every copy and launch costs
+    // enqueue time (numbers below); the two copy directions alone need 1.4 ms when overlapped (2 x 32 MiB each way at 2048^2 fp64).
     const int ny = s->ny;
     const int nb = std::max(1, std::min<int>({s->host_bands, (int) pf_solver::HOST_BANDS_MAX, ny / 64}));
     const int rows_per = (ny + nb - 1) / nb;
@@ -1467,22 +1466,30 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
         PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
         PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
     }
-    int bands = 0;
+    // Upload piece b ends `ghost` rows beyond band b, so that band b's inputs (its rows and `ghost` rows on either side) are on the
+    // device as soon as ITS piece is: compute b never waits for the whole next piece, and the downloads chain right behind the uploads.
+    // (Measured on the same box, 2048^2 fp64 explicit-rk4: 1.96 -> 1.89 ms per call at 8 bands; 4 bands 1.84, 16 bands 2.14: every band
+    // costs ~35 us of enqueue and copy set-up. Phi and T on two copy streams per direction: slower, 2.3 ms.)
+    const int ghost = pf_required_ghost(params->solver);
+    const int ny_up = ny - wrap_rows;                                            // the wrapped tail is already queued
+    int bands = 0, up0 = 0;
     for(int y0 = 0; y0 < ny; y0 += rows_per, bands++)
     {
-        const int y1 = std::min(ny - wrap_rows, y0 + rows_per);                 // the wrapped tail is already queued
-        const size_t off = (size_t) y0 * row_bytes, bytes = (size_t) std::max(0, y1 - y0) * row_bytes;
+        const int y1 = std::min(ny, y0 + rows_per);
+        const int up1 = std::max(up0, std::min(ny_up, y1 + ghost));
+        const size_t off = (size_t) up0 * row_bytes, bytes = (size_t)(up1 - up0) * row_bytes;
         if(bytes)
         {
             PF_CUDA(s, cudaMemcpyAsync(dF + off, (const char*) host_F + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
             PF_CUDA(s, cudaMemcpyAsync(dU + off, (const char*) host_U + off, bytes, cudaMemcpyHostToDevice, s->h2d_stream));
         }
         PF_CUDA(s, cudaEventRecord(s->ev_up[bands], s->h2d_stream));
+        up0 = up1;
     }
     for(int b = 0; b < bands; b++)
     {
         const int y0 = b * rows_per, y1 = std::min(ny, y0 + rows_per);
-        PF_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_up[std::min(b + 1, bands - 1)], 0));     // rows y1 .. y1+ghost live in the next band
+        PF_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_up[b], 0));
         {
             RowWindow w(s, y0, y1, 0);
             int rc = s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
