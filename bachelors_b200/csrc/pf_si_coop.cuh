@@ -69,6 +69,15 @@ __device__ __forceinline__ unsigned long long ll_load(const unsigned long long* 
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+// both words of a 16-byte slot in one access (a slot is 16-byte aligned; each word carries the tag, so tearing would be seen)
+__device__ __forceinline__ void ll_store2(unsigned long long* p, unsigned long long a, unsigned long long b)
+{
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" :: "l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ll_load2(const unsigned long long* p, unsigned long long& a, unsigned long long& b)
+{
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
 
 template <typename Real>
 struct GridSum {
@@ -96,8 +105,7 @@ struct GridSum {
             if constexpr (sizeof(Real) == 8)
             {
                 const unsigned long long bits = (unsigned long long) __double_as_longlong((double) block_val);
-                ll_store(set + 2 * blockIdx.x, tag | (bits & 0xffffffffull));
-                ll_store(set + 2 * blockIdx.x + 1, tag | (bits >> 32));
+                ll_store2(set + 2 * blockIdx.x, tag | (bits & 0xffffffffull), tag | (bits >> 32));
             }
             else ll_store(set + 2 * blockIdx.x, tag | (unsigned long long) __float_as_uint((float) block_val));
         }
@@ -108,15 +116,18 @@ struct GridSum {
             Real acc = 0;
             for(int i = threadIdx.x; i < nb; i += CG_THREADS)
             {
-                unsigned long long a;
-                do { a = ll_load(set + 2 * i); } while((unsigned)(a >> 32) != e);
                 if constexpr (sizeof(Real) == 8)
                 {
-                    unsigned long long b;
-                    do { b = ll_load(set + 2 * i + 1); } while((unsigned)(b >> 32) != e);
+                    unsigned long long a, b;
+                    do { ll_load2(set + 2 * i, a, b); } while((unsigned)(a >> 32) != e || (unsigned)(b >> 32) != e);
                     acc += (Real) __longlong_as_double((long long)((b << 32) | (a & 0xffffffffull)));
                 }
-                else acc += (Real) __uint_as_float((unsigned) a);
+                else
+                {
+                    unsigned long long a;
+                    do { a = ll_load(set + 2 * i); } while((unsigned)(a >> 32) != e);
+                    acc += (Real) __uint_as_float((unsigned) a);
+                }
             }
             acc = block_sum(acc, scratch);                                  // its __syncthreads orders all threads' polls before thread 0's fence
             if(threadIdx.x == 0)
@@ -128,23 +139,25 @@ struct GridSum {
                 if constexpr (sizeof(Real) == 8)
                 {
                     const unsigned long long bits = (unsigned long long) __double_as_longlong((double) acc);
-                    ll_store(out, tag | (bits & 0xffffffffull));
-                    ll_store(out + 1, tag | (bits >> 32));
+                    ll_store2(out, tag | (bits & 0xffffffffull), tag | (bits >> 32));
                 }
                 else ll_store(out, tag | (unsigned long long) __float_as_uint((float) acc));
             }
         }
         else if(threadIdx.x == 0)
         {
-            unsigned long long a;
-            do { a = ll_load(out); } while((unsigned)(a >> 32) != e);
             if constexpr (sizeof(Real) == 8)
             {
-                unsigned long long b;
-                do { b = ll_load(out + 1); } while((unsigned)(b >> 32) != e);
+                unsigned long long a, b;
+                do { ll_load2(out, a, b); } while((unsigned)(a >> 32) != e || (unsigned)(b >> 32) != e);
                 bcast = (Real) __longlong_as_double((long long)((b << 32) | (a & 0xffffffffull)));
             }
-            else bcast = (Real) __uint_as_float((unsigned) a);
+            else
+            {
+                unsigned long long a;
+                do { a = ll_load(out); } while((unsigned)(a >> 32) != e);
+                bcast = (Real) __uint_as_float((unsigned) a);
+            }
         }
         if(threadIdx.x == 0) ll_fence();                                    // acquire: loads after the barrier see what was stored before the flags
         __syncthreads();
