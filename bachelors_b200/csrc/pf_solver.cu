@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <mutex>
 
 #include "../../include/pf_solver.h"
 #include "pf_common.cuh"
@@ -1659,3 +1660,77 @@ int pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* o
 #include "pf_app_host.inl"
 #include "pf_si_slab.inl"
 #include "pf_halo.inl"
+
+// ---- pf_stats_delta_static: the delta statistics without any allocation ----------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it). The kernel is k_stats_delta, the one pf_stats_delta
+// launches; its per-block partials go into the file-scope device array below instead of the solver handle's cudaMalloc'ed buffer.
+// Every GPU that loads the library holds the array (PF_STATIC_STATS_MAX_BLOCKS x 40 B = 40 KB) until the process exits.
+// In HOST code `g_static_stats` is only a stand-in for the symbol, not a device address: the address is taken once per device,
+// with that device current, by cudaGetSymbolAddress, and that pointer is what the kernel gets.
+// All calls on a device share the array, which keeps the last call's contents. No word of it has to start at zero: a call
+// writes every slot it later reads (blocks 0 .. blocks-1), and the first thing a call does to a slot is overwrite it; the
+// slots beyond are never read. Calls that overlap on the GPU (two streams, two host threads) race on the slots.
+static __device__ __align__(256) pf::StatsPartial g_static_stats[PF_STATIC_STATS_MAX_BLOCKS];
+
+namespace {
+struct StaticStatsDevice { pf::StatsPartial* ptr = nullptr; int sm_count = 0; };
+enum { STATIC_STATS_MAX_DEVICES = 64 };
+StaticStatsDevice g_static_dev[STATIC_STATS_MAX_DEVICES];
+std::mutex g_static_mutex;
+
+// once per device, with that device current
+int static_stats_setup(int device, StaticStatsDevice* out)
+{
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticStatsDevice& d = g_static_dev[device];
+    if(!d.ptr)
+    {
+        pf::StatsPartial* ptr = nullptr; int sms = 0;
+        PF_CUDA(nullptr, cudaGetSymbolAddress((void**) &ptr, g_static_stats));
+        PF_CUDA(nullptr, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        if(!ptr || sms <= 0) return fail(nullptr, PF_ERR_CUDA, "pf_stats_delta_static: no address for the scratch array on device %d", device);
+        d.sm_count = sms; d.ptr = ptr;
+    }
+    *out = d;
+    return PF_OK;
+}
+
+template <typename Real>
+int stats_delta_static(const StaticStatsDevice& d, const Real* a, const Real* b, size_t N, cudaStream_t stream, pf_delta_stats* out)
+{
+    // the grid of stats_delta_device (elementwise_blocks, capped): same partials, same order of the final sum, same bits
+    const size_t want = (N + CG_THREADS - 1) / CG_THREADS, cap = (size_t) d.sm_count * 16;
+    const int blocks = (int) std::min<size_t>(PF_STATIC_STATS_MAX_BLOCKS, std::max<size_t>(1, std::min(want, cap)));
+    k_stats_delta<Real><<<blocks, CG_THREADS, 0, stream>>>(N, a, b, d.ptr);
+    { cudaError_t e = cudaGetLastError(); if(e != cudaSuccess) return fail(nullptr, PF_ERR_CUDA, "pf_stats_delta_static: launch failed: %s", cudaGetErrorString(e)); }
+    pf::StatsPartial h[PF_STATIC_STATS_MAX_BLOCKS];                                       // 40 KB of stack: nothing allocated on the host either
+    PF_CUDA(nullptr, cudaMemcpyAsync(h, d.ptr, blocks * sizeof(pf::StatsPartial), cudaMemcpyDeviceToHost, stream));
+    PF_CUDA(nullptr, cudaStreamSynchronize(stream));
+    Real sum = 0, L1 = 0, L2 = 0, mn = (Real) INFINITY, mx = -(Real) INFINITY;
+    for(int i = 0; i < blocks; i++)
+    {
+        sum += (Real) h[i].sum; L1 += (Real) h[i].L1; L2 += (Real) h[i].L2;
+        mn = std::min(mn, (Real) h[i].mn); mx = std::max(mx, (Real) h[i].mx);
+    }
+    out->sum = (double) sum; out->L1 = (double) L1; out->L2 = (double)(Real) sqrt((double) L2);
+    out->min = (double) mn; out->max = (double) mx;
+    return PF_OK;
+}
+} // namespace
+
+extern "C" int pf_stats_delta_static(int device, int dtype, const void* a, const void* b, size_t n, void* stream, pf_delta_stats* out)
+{
+    static_assert((int) PF_STATIC_STATS_MAX_BLOCKS == (int) CG_MAX_BLOCKS, "same grid cap as pf_stats_delta");
+    if(!a || !b || !out) return fail(nullptr, PF_ERR_INVALID, "pf_stats_delta_static: NULL argument");
+    if(dtype != PF_F32 && dtype != PF_F64) return fail(nullptr, PF_ERR_INVALID, "pf_stats_delta_static: bad dtype %d", dtype);
+    if(device < 0 || device >= STATIC_STATS_MAX_DEVICES) return fail(nullptr, PF_ERR_INVALID, "pf_stats_delta_static: bad device %d", device);
+    if(n == 0 || n > (size_t) PF_STATIC_STATS_MAX_ELEMS)
+        return fail(nullptr, PF_ERR_INVALID, "pf_stats_delta_static: n = %zu is outside 1 .. PF_STATIC_STATS_MAX_ELEMS = %zu (use pf_stats_delta for larger fields)",
+                    n, (size_t) PF_STATIC_STATS_MAX_ELEMS);
+    PF_CUDA(nullptr, cudaSetDevice(device));
+    StaticStatsDevice d;
+    if(int rc = static_stats_setup(device, &d)) return rc;
+    return dtype == PF_F64 ? stats_delta_static<double>(d, (const double*) a, (const double*) b, n, (cudaStream_t) stream, out)
+                           : stats_delta_static<float>(d, (const float*) a, (const float*) b, n, (cudaStream_t) stream, out);
+}

@@ -21,7 +21,7 @@ EXPORTS = [
     "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
     "pf_step", "pf_step_host", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
-    "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_halo_region", "pf_kernel_launches", "pf_bench_reductions",
+    "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_stats_delta_static", "pf_halo_region", "pf_kernel_launches", "pf_bench_reductions",
     "pf_init_fields", "pf_snapshot_begin", "pf_snapshot_wait", "pf_write_maps_bin", "pf_write_maps_bin_header",
     "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
     "pf_si_begin_async", "pf_si_partials", "pf_si_cg_begin_async", "pf_si_cg_spmv_async", "pf_si_cg_update_async",
@@ -75,6 +75,7 @@ def lib():
         "pf_cg_solve": (i32, [vp, P(pf_params), i32, vp, vp, vp, vp, dbl, i32, P(i32), P(i32), P(dbl)]),
         "pf_debug_values": (i32, [vp, P(pf_params), vp, vp, vp, vp, vp]),
         "pf_stats_delta": (i32, [vp, vp, vp, P(pf_delta_stats)]),
+        "pf_stats_delta_static": (i32, [i32, i32, vp, vp, sz, vp, P(pf_delta_stats)]),
         "pf_halo_region": (i32, [vp, vp, i32, P(vp), P(vp), P(sz)]),
         "pf_kernel_launches": (i64, [vp]),
         "pf_bench_reductions": (i32, [vp, sz, i32, i32, P(dbl), P(dbl), P(dbl)]),
@@ -298,6 +299,19 @@ class Solver:
         send, recv, n = C.c_void_p(), C.c_void_p(), C.c_size_t(0)
         self._ck(lib().pf_halo_region(self._h, field, side, C.byref(send), C.byref(recv), C.byref(n)))
         return send.value, recv.value, n.value
+
+
+def stats_delta_static(device, dtype, a, b, n, stream=None):
+    """pf_stats_delta_static: the delta statistics of a - b (device pointers, n values) through the entry point that allocates
+    nothing (scratch in a file-scope __device__ array; n <= PF_STATIC_STATS_MAX_ELEMS). No counterpart in the reference."""
+    out = pf_delta_stats()
+    rc = lib().pf_stats_delta_static(device, dtype, a, b, n, stream, C.byref(out))
+    if rc != PF_OK:
+        raise PfError(rc, lib().pf_last_error(None).decode())
+    return out
+
+
+PF_STATIC_STATS_MAX_ELEMS = 1 << 26
 
 
 # ---- output files of the reference host (pure host code in the library: usable without a GPU) -------------------

@@ -249,6 +249,17 @@ PF_API int  pf_debug_values(pf_solver* s, const pf_params* params, const void* F
 /* Delta statistics (cuda_stats_delta, cuda_reduction.cuh:391-407) of a - b. */
 PF_API int  pf_stats_delta(pf_solver* s, const void* a, const void* b, pf_delta_stats* out);
 
+/* pf_stats_delta for callers that cannot allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc. The same kernel and the same
+ * statistics as pf_stats_delta over n values of `dtype` (PF_F32 / PF_F64) at device pointers a, b on `device`, launched on
+ * `stream` (a cudaStream_t, NULL = the default stream); returns after the stream has finished the call. No solver handle and no
+ * cudaMalloc / cudaFree / allocating library call: the per-block partial sums live in a file-scope __device__ array of
+ * PF_STATIC_STATS_MAX_BLOCKS x 40 bytes (40 KB) that every GPU loading the library holds until the process exits.
+ * Limit: 1 <= n <= PF_STATIC_STATS_MAX_ELEMS (an 8192 x 8192 field), beyond that PF_ERR_INVALID with a message in
+ * pf_last_error(NULL). All calls on a device share the array: calls that overlap on the GPU race; serialise them. */
+enum { PF_STATIC_STATS_MAX_BLOCKS = 1024, PF_STATIC_STATS_MAX_ELEMS = 1 << 26 };
+PF_API int  pf_stats_delta_static(int device, int dtype, const void* a, const void* b, size_t n, void* stream, pf_delta_stats* out);
+
 /* ---- multi-GPU slabs ----------------------------------------------------- */
 /* Pointers/sizes of the rows a rank must SEND to / RECEIVE from a neighbour before a step:
  * side 0 = lo (rows below), 1 = hi. `send` = the first/last `ghost` OWNED rows, `recv` = the ghost rows.
