@@ -65,6 +65,10 @@ struct pf_solver {
     unsigned* run_progress = nullptr;       // multi-step launches: steps finished by each unit (+ 1 flag word), see StreamRun
     int run_progress_units = 0;
     unsigned run_base = 0;                  // progress value meaning "nothing of the next launch done yet"
+    // pf_run: RUN_GRAPH_STEPS single-launch steps (ping-pong baked in) captured once and replayed as a CUDA graph
+    cudaGraphExec_t run_graph = nullptr;
+    struct RunGraphKey { const void *F, *U, *nF, *nU; pf_params p; } run_graph_key = {};
+    bool run_graphs_ok = true;              // PF_OPT_RUN_GRAPHS; cleared when a capture fails
     int run_steps = 1;                      // steps the next fused launch advances (set by pf_run around its launch)
     bool run_used = false;                  // the last fused launch really was a multi-step launch
     int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
@@ -248,6 +252,7 @@ void pf_destroy(pf_solver* s)
     for(int i = 0; i < PF_SCRATCH_SLOTS; i++) if(s->scratch[i]) cudaFree(s->scratch[i]);
     if(s->partials) cudaFree(s->partials);
     if(s->ll_slots) cudaFree(s->ll_slots);
+    if(s->run_graph) cudaGraphExecDestroy(s->run_graph);
     if(s->run_progress) cudaFree(s->run_progress);
     if(s->halo_flags) cudaFree(s->halo_flags);
     if(s->d_cg) cudaFree(s->d_cg);
@@ -285,6 +290,7 @@ int pf_set_option(pf_solver* s, int option, int value)
         case PF_OPT_HOST_BANDS:    if(value < 1) return fail(s, PF_ERR_INVALID, "PF_OPT_HOST_BANDS: %d", value); s->host_bands = value; return PF_OK;
         case PF_OPT_SI_PER_KERNEL: s->force_per_kernel_cg = value != 0; return PF_OK;
         case PF_OPT_SI_GRID_SYNC:  s->plain_grid_sync = value != 0; return PF_OK;
+        case PF_OPT_RUN_GRAPHS:    s->run_graphs_ok = value != 0; return PF_OK;
         case PF_OPT_HALO_IN_KERNEL: s->halo_in_kernel_ok = value != 0; return PF_OK;
         default: return fail(s, PF_ERR_INVALID, "pf_set_option: unknown option %d", option);
     }
@@ -1320,6 +1326,44 @@ int pf_step_async(pf_solver* s, const pf_params* params, const void* F, const vo
                               : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
 }
 
+// pf_run's batches of single-launch steps (explicit Euler on the tile kernel; explicit-rk4 where the multi-step launch does not
+// apply): RUN_GRAPH_STEPS steps, the buffer ping-pong baked in (an even count: the replay ends where it began), captured once
+// per {buffers, parameters} and replayed. At 128^2 - 512^2 a step is a 2 - 3 us kernel behind a 2 - 4 us launch; the replay takes
+// the launches off the host. Nothing of a fused-eligible step depends on iter / time, so one capture serves the whole run.
+enum { RUN_GRAPH_STEPS = 64 };
+static int run_graph_prepare(pf_solver* s, const pf_params& p, void* cF, void* cU, void* nF, void* nU)
+{
+    pf_solver::RunGraphKey key; memset(&key, 0, sizeof key);
+    key.F = cF; key.U = cU; key.nF = nF; key.nU = nU; key.p = p; key.p.iter = 0; key.p.time = 0;
+    if(s->run_graph && memcmp(&key, &s->run_graph_key, sizeof key) == 0) return PF_OK;
+    if(s->run_graph) { cudaGraphExecDestroy(s->run_graph); s->run_graph = nullptr; }
+    const int64_t launches0 = s->launches;
+    cudaGraph_t g = nullptr;
+    PF_CUDA(s, cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = PF_OK;
+    void *a = cF, *b = cU, *c = nF, *d = nU;
+    for(int k = 0; k < RUN_GRAPH_STEPS && rc == PF_OK; k++)
+    {
+        pf_step_info info;
+        rc = s->dtype == PF_F64 ? step_impl<double>(s, p, a, b, c, d, &info, false) : step_impl<float>(s, p, a, b, c, d, &info, false);
+        std::swap(a, c); std::swap(b, d);
+    }
+    cudaError_t e = cudaStreamEndCapture(s->stream, &g);
+    const int64_t per_replay = s->launches - launches0;
+    s->launches = launches0;                                                // captured, not launched
+    if(rc == PF_OK && e == cudaSuccess && g && per_replay == RUN_GRAPH_STEPS) e = cudaGraphInstantiate(&s->run_graph, g, 0);
+    else if(e == cudaSuccess) e = cudaErrorUnknown;
+    if(g) cudaGraphDestroy(g);
+    if(e != cudaSuccess || !s->run_graph)
+    {
+        cudaGetLastError();                                                 // this handle goes on without graphs
+        s->run_graph = nullptr; s->run_graphs_ok = false;
+        return PF_OK;
+    }
+    memcpy(&s->run_graph_key, &key, sizeof key);
+    return PF_OK;
+}
+
 int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
            void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info)
 {
@@ -1347,6 +1391,7 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
             while(i + batch < n_steps && batch < (1 << 20) && !(stop_time > 0 && stop_time - tt < 1e-16)) { tt += p.dt; batch++; }
         }
         pf_step_info info;
+        int64_t graph_steps = 0;
         if(batch > 1)
         {
             s->run_steps = (int) batch;
@@ -1362,6 +1407,7 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
                 continue;
             }
             // the grid does not fit one wave (or the device cannot launch cooperatively): that was a plain single step
+            if(s->run_graphs_ok) graph_steps = (batch - 1) / RUN_GRAPH_STEPS * RUN_GRAPH_STEPS;
         }
         else
         {
@@ -1374,6 +1420,20 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
         if(last_info) *last_info = info;
         std::swap(cF, nF); std::swap(cU, nU);
         i++;
+        if(graph_steps > 0)
+        {
+            if(int rc = run_graph_prepare(s, p, cF, cU, nF, nU)) return rc;
+            if(s->run_graph)
+            {
+                for(int64_t k = 0; k < graph_steps; k += RUN_GRAPH_STEPS)
+                {
+                    PF_CUDA(s, cudaGraphLaunch(s->run_graph, s->stream));
+                    s->launches += RUN_GRAPH_STEPS;
+                }
+                for(int64_t k = 0; k < graph_steps; k++) t += info.dt_advanced;   // the same floating-point additions as step by step
+                i += graph_steps;                                                  // an even number of steps: the buffers are where they were
+            }
+        }
     }
     PF_CUDA(s, cudaStreamSynchronize(s->stream));
     if(s->run_progress)

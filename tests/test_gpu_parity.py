@@ -12,7 +12,7 @@ import pytest
 
 from bachelors_b200 import solver as S
 from bachelors_b200._abi import (PF_ERR_INVALID, PF_ERR_UNSUPPORTED, PF_F32, PF_F64, PF_OPT_HOST_BANDS, PF_OPT_SI_GRID_SYNC,
-                                 PF_OPT_SI_PER_KERNEL, default_params, pf_slab)
+                                 PF_OPT_SI_PER_KERNEL, PF_OPT_RUN_GRAPHS, default_params, pf_slab)
 from bachelors_b200.config import read_config
 from bachelors_b200.initial import make_initial_conditions
 from bachelors_b200.testing import seeded_fields
@@ -299,6 +299,38 @@ def test_run_is_one_multi_step_launch_with_the_bits_of_single_steps(solver, size
         Fo2, Uo2, done2, _, _ = s.run(p, Fo, Uo, tF if Fo == F else F, tU if Uo == U else U, 3)
         ref2 = cuda_replay(p, ref[0], ref[1], dtype, 3)
         assert done2 == 3 and np.array_equal(s.download(Fo2), ref2[0]) and np.array_equal(s.download(Uo2), ref2[1])
+
+
+@pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
+@pytest.mark.parametrize("solver,size,steps", [("explicit", (128, 128), 134), ("explicit", (300, 171), 200), ("explicit", (512, 512), 65),
+                                               ("explicit-rk4", (96, 40), 150)])
+def test_run_replays_single_launch_steps_as_cuda_graphs(solver, size, steps, dtype):
+    """pf_run of the fixed-step solvers whose step is one launch (explicit Euler; explicit-rk4 on grids too small for the
+    multi-step launch): batches of 64 steps are captured once and replayed as a CUDA graph (PF_OPT_RUN_GRAPHS, default on).
+    Same bits, same step count, same time and the same number of kernels as with the graphs switched off, also when a second
+    run continues with the buffers in the other orientation and when a stop time cuts the batch."""
+    nx, ny = size
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=max(nx, ny) / 128.0, S=0.2)
+    npdt = np.float64 if dtype == PF_F64 else np.float32
+    F0, U0 = seeded_fields(nx, ny, npdt, kind="interface")
+
+    def run(graphs):
+        with S.Solver(nx, ny, dtype) as s:
+            s.set_option(PF_OPT_RUN_GRAPHS, graphs)
+            F, U, tF, tU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+            l0 = s.kernel_launches
+            Fo, Uo, done, t, _ = s.run(p, F, U, tF, tU, steps)
+            q = p.copy(); q.iter, q.time = p.iter + done, p.time + t
+            oF, oU = (tF, tU) if Fo == F else (F, U)
+            Fo2, Uo2, done2, t2, _ = s.run(q, Fo, Uo, oF, oU, 10 ** 6, stop_time=q.time + 70.5 * p.dt)     # 71 steps, then the stop time
+            return s.download(Fo2), s.download(Uo2), done, done2, t, t2, s.kernel_launches - l0, Fo == (tF if steps % 2 else F)
+
+    gF, gU, gdone, gdone2, gt, gt2, glaunch, gorient = run(1)
+    pF, pU, pdone, pdone2, pt, pt2, plaunch, porient = run(0)
+    assert (gdone, gdone2) == (steps, 71) == (pdone, pdone2) and gorient and porient
+    assert gt == pt and gt2 == pt2
+    assert glaunch == plaunch == steps + 71
+    assert np.isfinite(gF).all() and np.array_equal(gF, pF) and np.array_equal(gU, pU)
 
 
 @pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
