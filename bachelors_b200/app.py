@@ -189,6 +189,18 @@ def run_config(config_path, dtype=PF_F64, device=0, overrides=(), png=False, log
                 assert done == n
                 it += n
                 sim_time = t
+            elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not collect:
+                # the step sizes are the solver's: pf_run_until steps until one of the three tests at the loop head would fire
+                # (its t_end is this loop's sim_time: the same additions in the same order)
+                next_every = (snapshot_every_i + 1) * cfg.snapshot_every
+                next_times = (snapshot_times_i + 1) * stop / cfg.snapshot_times if cfg.snapshot_times else float("inf")
+                pause = min(next_every, next_times)
+                four = (F, U, F2, U2)
+                F, U, done, _adv, _ = sol.run(params, F, U, F2, U2, (1 << 40) if pause > sim_time else 1, stop_time=stop,
+                                              pause_time=pause if pause != float("inf") and pause > 0 else 0.0)
+                F2, U2 = [f for f in four if f not in (F, U)]
+                it += done
+                sim_time = sol.last_run_end_time
             else:
                 info = sol.step(params, F, U, F2, U2)
                 sim_time += info.dt_advanced

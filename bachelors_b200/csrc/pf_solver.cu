@@ -1367,6 +1367,12 @@ static int run_graph_prepare(pf_solver* s, const pf_params& p, void* cF, void* c
 int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
            void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info)
 {
+    return pf_run_until(s, params, F, U, F_tmp, U_tmp, n_steps, stop_time, 0.0, F_out, U_out, steps_done, t_advanced, nullptr, last_info);
+}
+
+int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
+                 double pause_time, void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, pf_step_info* last_info)
+{
     if(int rc = bind(s)) return rc;
     if(int rc = check_step_args(s, params, F, U, F_tmp, U_tmp)) return rc;
     pf_params p = *params;
@@ -1381,6 +1387,7 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
     while(i < n_steps)
     {
         if(stop_time > 0 && stop_time - t < 1e-16) break;                  // main.cpp:525
+        if(pause_time > 0 && i > 0 && t >= pause_time) break;              // the host's snapshot tests (main.cpp:507-520) would fire: hand back
         p.iter = params->iter + i; p.time = t;
         int64_t batch = 1;
         if(multi_ok)
@@ -1446,6 +1453,7 @@ int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp,
     if(U_out) *U_out = cU;
     if(steps_done) *steps_done = i;
     if(t_advanced) *t_advanced = t - params->time;
+    if(t_end) *t_end = t;                                                   // params->time + dt + dt + ...: the host loop's own additions
     return PF_OK;
 }
 

@@ -20,7 +20,7 @@ EXPORTS = [
     "pf_field_alloc", "pf_field_free", "pf_field_rows", "pf_upload", "pf_download", "pf_upload_raw", "pf_download_raw",
     "pf_aux_stream", "pf_step_rows_async", "pf_rkm_attempt_rows_async", "pf_rkm_clear_errors_async",
     "pf_rkm_begin", "pf_rkm_attempt_async", "pf_rkm_error_bits", "pf_rkm_decide", "pf_rkm_finish_async",
-    "pf_step", "pf_step_host", "pf_run", "pf_step_async", "pf_sync", "pf_stream",
+    "pf_step", "pf_step_host", "pf_run", "pf_run_until", "pf_step_async", "pf_sync", "pf_stream",
     "pf_rhs", "pf_cg_solve", "pf_debug_values", "pf_stats_delta", "pf_stats_delta_static", "pf_halo_region", "pf_kernel_launches", "pf_bench_reductions",
     "pf_init_fields", "pf_snapshot_begin", "pf_snapshot_wait", "pf_write_maps_bin", "pf_write_maps_bin_header",
     "pf_write_maps_bin_rows", "pf_write_stats_csv", "pf_render_rgba", "pf_write_png",
@@ -70,6 +70,7 @@ def lib():
         "pf_step": (i32, [vp, P(pf_params), vp, vp, vp, vp, P(pf_step_info)]),
         "pf_step_host": (i32, [vp, P(pf_params), vp, vp, vp, vp, i32, vp, vp, vp, vp, P(pf_step_info)]),
         "pf_run": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, P(vp), P(vp), P(i64), P(dbl), P(pf_step_info)]),
+        "pf_run_until": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, dbl, P(vp), P(vp), P(i64), P(dbl), P(dbl), P(pf_step_info)]),
         "pf_step_async": (i32, [vp, P(pf_params), vp, vp, vp, vp]), "pf_sync": (i32, [vp]), "pf_stream": (vp, [vp]),
         "pf_rhs": (i32, [vp, P(pf_params), i32, P(dbl), P(vp), P(vp), vp, vp]),
         "pf_cg_solve": (i32, [vp, P(pf_params), i32, vp, vp, vp, vp, dbl, i32, P(i32), P(i32), P(dbl)]),
@@ -211,11 +212,13 @@ class Solver:
     def step_async(self, params, F, U, next_F, next_U):
         self._ck(lib().pf_step_async(self._h, C.byref(params), F, U, next_F, next_U))
 
-    def run(self, params, F, U, F_tmp, U_tmp, n_steps, stop_time=0.0):
+    def run(self, params, F, U, F_tmp, U_tmp, n_steps, stop_time=0.0, pause_time=0.0):
         Fo, Uo, done, t = C.c_void_p(), C.c_void_p(), C.c_int64(0), C.c_double(0)
         info = pf_step_info()
-        self._ck(lib().pf_run(self._h, C.byref(params), F, U, F_tmp, U_tmp, n_steps, stop_time,
-                              C.byref(Fo), C.byref(Uo), C.byref(done), C.byref(t), C.byref(info)))
+        t_end = C.c_double(0)
+        self._ck(lib().pf_run_until(self._h, C.byref(params), F, U, F_tmp, U_tmp, n_steps, stop_time, pause_time,
+                                    C.byref(Fo), C.byref(Uo), C.byref(done), C.byref(t), C.byref(t_end), C.byref(info)))
+        self.last_run_end_time = t_end.value                                # params.time + dt + dt + ...: the host loop's sim_time
         return Fo.value, Uo.value, done.value, t.value, info
 
     def sync(self):

@@ -188,6 +188,14 @@ PF_API int  pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void
                    int64_t n_steps, double stop_time,
                    void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info);
 
+/* pf_run that also hands back after the first step that reaches pause_time (params->time + advanced >= pause_time, checked
+ * after every step but not before the first; 0 = never): the host's snapshot tests (main.cpp:507-520) for solvers whose
+ * step size is not known in advance - the adaptive solver's whole interval between two snapshots in one call.
+ * *t_end = params->time + dt_1 + dt_2 + ... added in this order: bit for bit the sim_time of the host loop (main.cpp:553). */
+PF_API int  pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp,
+                         int64_t n_steps, double stop_time, double pause_time,
+                         void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, pf_step_info* last_info);
+
 /* The reference host's per-step sequence with HOST fields as ONE call: sim_modify(F, UPLOAD), sim_modify(U, UPLOAD)
  * (main.cpp:164-168), sim_step (main.cpp:553), sim_modify(next_F, DOWNLOAD), sim_modify(next_U, DOWNLOAD) (main.cpp:857).
  * host_F / host_U (y(n)) and host_next_F / host_next_U (y(n+1)) are dense nx x ny_local arrays of host_dtype (pinned memory
