@@ -142,7 +142,10 @@ def run_config(config_path, dtype=PF_F64, device=0, overrides=(), png=False, log
         snapshot_every_i = snapshot_times_i = 0
         end_reached = False
         collect = bool(cfg.app_collect_stats)
-        batched = p.solver != SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not collect
+        # per-step residuals of the corrector loop need every step's info; plain delta statistics are wanted only for the step that
+        # crosses the next collection time (main.cpp:554-555): pf_run_until hands back there, with that step's statistics
+        per_step = collect and bool(cfg.app_collect_step_residuals)
+        batched = p.solver != SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not per_step
         last_stats_save = 0.0                                                   # app->last_stats_save: set by every collection (main.cpp:233)
         t0 = time.perf_counter()
 
@@ -181,26 +184,36 @@ def run_config(config_path, dtype=PF_F64, device=0, overrides=(), png=False, log
                 while True:
                     t += p.dt
                     n += 1
-                    if save_due(t):
+                    if save_due(t) or (collect and t >= last_stats_save + cfg.app_collect_stats_every):
                         break
                 four = (F, U, F2, U2)
-                F, U, done, _adv, _ = sol.run(params, F, U, F2, U2, n)
+                F, U, done, _adv, info = sol.run(params, F, U, F2, U2, n)
                 F2, U2 = [f for f in four if f not in (F, U)]           # the other two allocations are the scratch pair now
                 assert done == n
                 it += n
                 sim_time = t
-            elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not collect:
+                if collect and sim_time >= last_stats_save + cfg.app_collect_stats_every:      # main.cpp:554-555
+                    q = params.copy(); q.iter, q.time = it - 1, sol.last_run_last_step_time
+                    stats_rows.append(_stats_row(q, info))
+                    last_stats_save = sim_time
+            elif p.solver == SOLVER_TYPE_EXPLICIT_RK4_ADAPTIVE and not per_step:
                 # the step sizes are the solver's: pf_run_until steps until one of the three tests at the loop head would fire
                 # (its t_end is this loop's sim_time: the same additions in the same order)
                 next_every = (snapshot_every_i + 1) * cfg.snapshot_every
                 next_times = (snapshot_times_i + 1) * stop / cfg.snapshot_times if cfg.snapshot_times else float("inf")
                 pause = min(next_every, next_times)
+                if collect:
+                    pause = min(pause, last_stats_save + cfg.app_collect_stats_every)
                 four = (F, U, F2, U2)
-                F, U, done, _adv, _ = sol.run(params, F, U, F2, U2, (1 << 40) if pause > sim_time else 1, stop_time=stop,
+                F, U, done, _adv, info = sol.run(params, F, U, F2, U2, (1 << 40) if pause > sim_time else 1, stop_time=stop,
                                               pause_time=pause if pause != float("inf") and pause > 0 else 0.0)
                 F2, U2 = [f for f in four if f not in (F, U)]
                 it += done
                 sim_time = sol.last_run_end_time
+                if collect and sim_time >= last_stats_save + cfg.app_collect_stats_every:      # main.cpp:554-555
+                    q = params.copy(); q.iter, q.time = it - 1, sol.last_run_last_step_time
+                    stats_rows.append(_stats_row(q, info))
+                    last_stats_save = sim_time
             else:
                 info = sol.step(params, F, U, F2, U2)
                 sim_time += info.dt_advanced

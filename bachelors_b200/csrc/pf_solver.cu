@@ -1367,18 +1367,24 @@ static int run_graph_prepare(pf_solver* s, const pf_params& p, void* cF, void* c
 int pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
            void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, pf_step_info* last_info)
 {
-    return pf_run_until(s, params, F, U, F_tmp, U_tmp, n_steps, stop_time, 0.0, F_out, U_out, steps_done, t_advanced, nullptr, last_info);
+    return pf_run_until(s, params, F, U, F_tmp, U_tmp, n_steps, stop_time, 0.0, F_out, U_out, steps_done, t_advanced, nullptr, nullptr, last_info);
 }
 
 int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp, int64_t n_steps, double stop_time,
-                 double pause_time, void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, pf_step_info* last_info)
+                 double pause_time, void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, double* t_last_begin,
+                 pf_step_info* last_info)
 {
     if(int rc = bind(s)) return rc;
     if(int rc = check_step_args(s, params, F, U, F_tmp, U_tmp)) return rc;
     pf_params p = *params;
     void *cF = F, *cU = U, *nF = F_tmp, *nU = U_tmp;
-    double t = params->time;
+    double t = params->time, t_before_last = params->time;
     int64_t i = 0;
+    // The delta statistics (simulation.cu:1126-1142) of every step but the last would be thrown away (one pf_step_info comes
+    // back): the steps run without them, on the fast paths, and the last step's statistics are formed after the loop from the
+    // two buffers of the ping-pong - the state before the last step is still in the other one.
+    const bool want_stats = p.do_stats != 0 && !p.do_stats_step_residual;
+    if(want_stats) p.do_stats = 0;
     // fixed-dt solvers without statistics never need the host between steps: enqueue everything, synchronise once
     const bool async_ok = p.solver != PF_SOLVER_EXPLICIT_RK4_ADAPTIVE && !p.do_stats && !p.do_stats_step_residual;
     // the fixed-step explicit solvers on the single-kernel path: ONE launch per batch of steps (k_stream_step, StreamRun)
@@ -1395,7 +1401,8 @@ int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* 
             // how many steps until the stop time (the same additions of dt the loop below would make), at most 2^20 per launch
             double tt = t;
             batch = 0;
-            while(i + batch < n_steps && batch < (1 << 20) && !(stop_time > 0 && stop_time - tt < 1e-16)) { tt += p.dt; batch++; }
+            while(i + batch < n_steps && batch < (1 << 20) && !(stop_time > 0 && stop_time - tt < 1e-16) &&
+                  !(pause_time > 0 && i + batch > 0 && tt >= pause_time)) { tt += p.dt; batch++; }
         }
         pf_step_info info;
         int64_t graph_steps = 0;
@@ -1407,7 +1414,7 @@ int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* 
             if(rc) return rc;
             if(s->run_used)
             {
-                for(int64_t k = 0; k < batch; k++) t += info.dt_advanced;    // the same floating-point additions as step by step
+                for(int64_t k = 0; k < batch; k++) { t_before_last = t; t += info.dt_advanced; }   // the same floating-point additions as step by step
                 i += batch;
                 if(batch & 1) { std::swap(cF, nF); std::swap(cU, nU); }
                 if(last_info) *last_info = info;
@@ -1423,6 +1430,7 @@ int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* 
                                         : step_impl<float>(s, p, cF, cU, nF, nU, &info, !async_ok || last);
             if(rc) return rc;
         }
+        t_before_last = t;
         t += info.dt_advanced;
         if(last_info) *last_info = info;
         std::swap(cF, nF); std::swap(cU, nU);
@@ -1437,7 +1445,7 @@ int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* 
                     PF_CUDA(s, cudaGraphLaunch(s->run_graph, s->stream));
                     s->launches += RUN_GRAPH_STEPS;
                 }
-                for(int64_t k = 0; k < graph_steps; k++) t += info.dt_advanced;   // the same floating-point additions as step by step
+                for(int64_t k = 0; k < graph_steps; k++) { t_before_last = t; t += info.dt_advanced; }   // the same floating-point additions as step by step
                 i += graph_steps;                                                  // an even number of steps: the buffers are where they were
             }
         }
@@ -1449,10 +1457,20 @@ int pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* 
         PF_CUDA(s, cudaMemcpy(&stalled, s->run_progress + s->run_progress_units, sizeof stalled, cudaMemcpyDeviceToHost));
         if(stalled) { cudaMemset(s->run_progress + s->run_progress_units, 0, sizeof stalled); return fail(s, PF_ERR_CUDA, "pf_run: a multi-step launch stalled (its CTAs were not co-resident)"); }
     }
+    if(want_stats && i > 0 && last_info)
+    {
+        int rc;
+        if(s->dtype == PF_F64) { rc = stats_delta_device<double>(s, (const double*) nF, (const double*) cF, &last_info->Phi_delta);
+                                 if(!rc) rc = stats_delta_device<double>(s, (const double*) nU, (const double*) cU, &last_info->T_delta); }
+        else                   { rc = stats_delta_device<float>(s, (const float*) nF, (const float*) cF, &last_info->Phi_delta);
+                                 if(!rc) rc = stats_delta_device<float>(s, (const float*) nU, (const float*) cU, &last_info->T_delta); }
+        if(rc) return rc;
+    }
     if(F_out) *F_out = cF;
     if(U_out) *U_out = cU;
     if(steps_done) *steps_done = i;
     if(t_advanced) *t_advanced = t - params->time;
+    if(t_last_begin) *t_last_begin = t_before_last;                         // the time the last step started from (its stats row, main.cpp:192-234)
     if(t_end) *t_end = t;                                                   // params->time + dt + dt + ...: the host loop's own additions
     return PF_OK;
 }

@@ -70,7 +70,7 @@ def lib():
         "pf_step": (i32, [vp, P(pf_params), vp, vp, vp, vp, P(pf_step_info)]),
         "pf_step_host": (i32, [vp, P(pf_params), vp, vp, vp, vp, i32, vp, vp, vp, vp, P(pf_step_info)]),
         "pf_run": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, P(vp), P(vp), P(i64), P(dbl), P(pf_step_info)]),
-        "pf_run_until": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, dbl, P(vp), P(vp), P(i64), P(dbl), P(dbl), P(pf_step_info)]),
+        "pf_run_until": (i32, [vp, P(pf_params), vp, vp, vp, vp, i64, dbl, dbl, P(vp), P(vp), P(i64), P(dbl), P(dbl), P(dbl), P(pf_step_info)]),
         "pf_step_async": (i32, [vp, P(pf_params), vp, vp, vp, vp]), "pf_sync": (i32, [vp]), "pf_stream": (vp, [vp]),
         "pf_rhs": (i32, [vp, P(pf_params), i32, P(dbl), P(vp), P(vp), vp, vp]),
         "pf_cg_solve": (i32, [vp, P(pf_params), i32, vp, vp, vp, vp, dbl, i32, P(i32), P(i32), P(dbl)]),
@@ -215,9 +215,10 @@ class Solver:
     def run(self, params, F, U, F_tmp, U_tmp, n_steps, stop_time=0.0, pause_time=0.0):
         Fo, Uo, done, t = C.c_void_p(), C.c_void_p(), C.c_int64(0), C.c_double(0)
         info = pf_step_info()
-        t_end = C.c_double(0)
+        t_end, t_last = C.c_double(0), C.c_double(0)
         self._ck(lib().pf_run_until(self._h, C.byref(params), F, U, F_tmp, U_tmp, n_steps, stop_time, pause_time,
-                                    C.byref(Fo), C.byref(Uo), C.byref(done), C.byref(t), C.byref(t_end), C.byref(info)))
+                                    C.byref(Fo), C.byref(Uo), C.byref(done), C.byref(t), C.byref(t_end), C.byref(t_last), C.byref(info)))
+        self.last_run_last_step_time = t_last.value                         # the time the last step started from
         self.last_run_end_time = t_end.value                                # params.time + dt + dt + ...: the host loop's sim_time
         return Fo.value, Uo.value, done.value, t.value, info
 

@@ -191,10 +191,14 @@ PF_API int  pf_run(pf_solver* s, const pf_params* params, void* F, void* U, void
 /* pf_run that also hands back after the first step that reaches pause_time (params->time + advanced >= pause_time, checked
  * after every step but not before the first; 0 = never): the host's snapshot tests (main.cpp:507-520) for solvers whose
  * step size is not known in advance - the adaptive solver's whole interval between two snapshots in one call.
- * *t_end = params->time + dt_1 + dt_2 + ... added in this order: bit for bit the sim_time of the host loop (main.cpp:553). */
+ * *t_end = params->time + dt_1 + dt_2 + ... added in this order: bit for bit the sim_time of the host loop (main.cpp:553);
+ * *t_last_begin = the same sum without the last step (the time of its statistics row). With params->do_stats (and no
+ * do_stats_step_residual) the steps run WITHOUT statistics on the fast paths, and last_info carries the delta statistics of
+ * the last step, formed after the loop from the two ping-pong buffers - the only ones a caller of this function can see. */
 PF_API int  pf_run_until(pf_solver* s, const pf_params* params, void* F, void* U, void* F_tmp, void* U_tmp,
                          int64_t n_steps, double stop_time, double pause_time,
-                         void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, pf_step_info* last_info);
+                         void** F_out, void** U_out, int64_t* steps_done, double* t_advanced, double* t_end, double* t_last_begin,
+                         pf_step_info* last_info);
 
 /* The reference host's per-step sequence with HOST fields as ONE call: sim_modify(F, UPLOAD), sim_modify(U, UPLOAD)
  * (main.cpp:164-168), sim_step (main.cpp:553), sim_modify(next_F, DOWNLOAD), sim_modify(next_U, DOWNLOAD) (main.cpp:857).

@@ -333,6 +333,43 @@ def test_run_replays_single_launch_steps_as_cuda_graphs(solver, size, steps, dty
     assert np.isfinite(gF).all() and np.array_equal(gF, pF) and np.array_equal(gU, pU)
 
 
+@pytest.mark.parametrize("solver,size,steps", [("explicit-rk4", (1200, 1030), 7), ("explicit", (300, 171), 70), ("explicit-rk4-adaptive", (200, 136), 5),
+                                               ("semi-implicit", (160, 128), 4)])
+def test_run_with_statistics_keeps_the_fast_paths(solver, size, steps):
+    """pf_run / pf_run_until with do_stats: the steps run without statistics (explicit-rk4: still ONE multi-step launch, explicit:
+    still the graph replay) and last_info carries the delta statistics of the LAST step, formed after the loop from the two
+    ping-pong buffers - bit for bit what pf_step with do_stats returns for that step, with the same fields."""
+    nx, ny = size
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=max(nx, ny) / 128.0, S=0.2)
+    if solver == "explicit-rk4-adaptive":
+        p.T_tolerance = p.Phi_tolerance = 1e-7
+    p.do_stats = 1
+    F0, U0 = seeded_fields(nx, ny, np.float64, kind="interface")
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        q, t = p.copy(), p.time
+        for i in range(steps):
+            q.iter, q.time = p.iter + i, t
+            info = s.step(q, F, U, nF, nU)
+            t += info.dt_advanced
+            F, nF, U, nU = nF, F, nU, U
+        want = (s.download(F), s.download(U), t)
+        want_stats = [(d.sum, d.L1, d.L2, d.min, d.max) for d in (info.Phi_delta, info.T_delta)]
+    with S.Solver(nx, ny, PF_F64) as s:
+        F, U, nF, nU = s.field_from(F0), s.field_from(U0), s.field_alloc(), s.field_alloc()
+        l0 = s.kernel_launches
+        Fo, Uo, done, _, rinfo = s.run(p, F, U, nF, nU, steps)
+        launches = s.kernel_launches - l0
+        assert done == steps and s.last_run_end_time == want[2]
+        assert np.array_equal(s.download(Fo), want[0]) and np.array_equal(s.download(Uo), want[1])
+        got_stats = [(d.sum, d.L1, d.L2, d.min, d.max) for d in (rinfo.Phi_delta, rinfo.T_delta)]
+        assert got_stats == want_stats and want_stats[0][1] > 0
+        if solver == "explicit-rk4":
+            assert launches == 1 + 2                                       # the multi-step launch + the two statistics kernels
+        if solver == "explicit":
+            assert launches == steps + 2
+
+
 @pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
 @pytest.mark.parametrize("variant", ["guess_periodic", "neumann_dirichlet", "dirichlet_neumann_aniso_guess", "corrector_loop", "corrector_loop_mixed", "exact_source"])
 def test_euler_parameter_space_is_one_launch_per_rhs(variant, dtype):
