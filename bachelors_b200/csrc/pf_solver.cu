@@ -1514,7 +1514,7 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
     char *dF = (char*) F + first * rs, *dU = (char*) U + first * rs, *dnF = (char*) next_F + first * rs, *dnU = (char*) next_U + first * rs;
     const bool pipelined = host_dtype == s->dtype && s->is_full_grid() &&
         (params->solver == PF_SOLVER_EXPLICIT_EULER || params->solver == PF_SOLVER_EXPLICIT_RK4) &&
-        !params->do_corrector_loop && !params->do_stats && !params->do_stats_step_residual && fused_eligible(s, *params) &&
+        !params->do_corrector_loop && !params->do_stats_step_residual && fused_eligible(s, *params) &&
         (s->last_num_steps % 2) == 0 && s->ny >= 64;
     if(!pipelined)
     {
@@ -1559,6 +1559,7 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
     // costs ~35 us of enqueue and copy set-up. Phi and T on two copy streams per direction: slower, 2.3 ms.)
     const int ghost = pf_required_ghost(params->solver);
     const int ny_up = ny - wrap_rows;                                            // the wrapped tail is already queued
+    pf_params band_params = *params; band_params.do_stats = 0;            // the statistics are formed once, after the last band (below)
     int bands = 0, up0 = 0;
     for(int y0 = 0; y0 < ny; y0 += rows_per, bands++)
     {
@@ -1579,8 +1580,8 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
         PF_CUDA(s, cudaStreamWaitEvent(s->stream, s->ev_up[b], 0));
         {
             RowWindow w(s, y0, y1, 0);
-            int rc = s->dtype == PF_F64 ? step_impl<double>(s, *params, F, U, next_F, next_U, nullptr, false)
-                                        : step_impl<float>(s, *params, F, U, next_F, next_U, nullptr, false);
+            int rc = s->dtype == PF_F64 ? step_impl<double>(s, band_params, F, U, next_F, next_U, nullptr, false)
+                                        : step_impl<float>(s, band_params, F, U, next_F, next_U, nullptr, false);
             if(rc) return rc;
         }
         PF_CUDA(s, cudaEventRecord(s->ev_done[b], s->stream));
@@ -1596,6 +1597,15 @@ int pf_step_host(pf_solver* s, const pf_params* params, const void* host_F, cons
         memset(info, 0, sizeof *info);
         info->dt_advanced = params->dt;
         info->Phi_iters = 1; info->T_iters = 1;
+        if(params->do_stats)                                                // simulation.cu:1126-1142, on the fields that are now both on the device
+        {
+            int rc;
+            if(s->dtype == PF_F64) { rc = stats_delta_device<double>(s, (const double*) F, (const double*) next_F, &info->Phi_delta);
+                                     if(!rc) rc = stats_delta_device<double>(s, (const double*) U, (const double*) next_U, &info->T_delta); }
+            else                   { rc = stats_delta_device<float>(s, (const float*) F, (const float*) next_F, &info->Phi_delta);
+                                     if(!rc) rc = stats_delta_device<float>(s, (const float*) U, (const float*) next_U, &info->T_delta); }
+            if(rc) return rc;
+        }
     }
     return PF_OK;
 }

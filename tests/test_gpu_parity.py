@@ -628,7 +628,8 @@ def test_step_host_equals_upload_step_download(solver, dtype, host_dtype, bc):
         bF, bU, bnF, bnU = b.field_alloc(), b.field_alloc(), b.field_alloc(), b.field_alloc()
         hF, hU = F0.copy(), U0.copy()
         gF, gU = F0.copy(), U0.copy()
-        for _ in range(3):
+        for it in range(3):
+            p.do_stats = int(it == 2)                                   # the pipelined path keeps running; statistics after the last band
             oF, oU = np.empty_like(hF), np.empty_like(hU)
             L = S.lib()
             info = S.pf_step_info()
@@ -640,6 +641,9 @@ def test_step_host_equals_upload_step_download(solver, dtype, host_dtype, bc):
             wF, wU = b.download(bnF, dtype=npdt), b.download(bnU, dtype=npdt)
             assert np.array_equal(oF, wF) and np.array_equal(oU, wU)
             assert info.dt_advanced == winfo.dt_advanced and info.Phi_iters == winfo.Phi_iters
+            if p.do_stats and host_dtype == dtype:
+                for d, w in ((info.Phi_delta, winfo.Phi_delta), (info.T_delta, winfo.T_delta)):
+                    assert (d.sum, d.L1, d.L2, d.min, d.max) == (w.sum, w.L1, w.L2, w.min, w.max) and w.L1 > 0
             hF, hU, gF, gU = oF, oU, wF, wU
             aF, anF, aU, anU = anF, aF, anU, aU
             bF, bnF, bU, bnU = bnF, bF, bnU, bU
