@@ -491,7 +491,11 @@ static int launch_tiled(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
 // CTA = 4 warps (128 columns, 128 - 2*NST of them interior). Resident CTAs per SM by register budget:
 // Euler 8 (<= 64 registers), the multi-stage schemes 4 (<= 128 registers).
 enum { STREAM_WARPS = 4 };
-template <int SCHEME, bool ANISO> struct StreamOcc { static constexpr int MINB = SCHEME == SCHEME_EULER ? (ANISO ? 6 : 8) : 4; };
+// Resident CTAs per SM the streaming kernels are compiled for. Merson in fp64 needs 148 - 164 registers: at 4 CTAs (128 registers)
+// it spills 64 - 136 bytes per thread into the row loop; at 3 CTAs it does not (2048^2 adaptive step 129.7 -> 121.5 us, same bits).
+template <typename Real, int SCHEME, bool ANISO> struct StreamOcc {
+    static constexpr int MINB = SCHEME == SCHEME_EULER ? (ANISO ? 6 : 8) : (SCHEME == SCHEME_RKM && sizeof(Real) == 8 ? 3 : 4);
+};
 
 // Number of row chunks: every CTA marches down its chunk plus a pipeline fill of 2(NST-1) rows, so few long
 // chunks waste the least work, but the grid should fill the machine's resident-CTA slots in whole waves. Cost model
@@ -518,7 +522,7 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
 template <typename Real, int SCHEME, bool ANISO>
 static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
 {
-    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, MINB = StreamOcc<SCHEME, ANISO>::MINB;
+    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, MINB = StreamOcc<Real, SCHEME, ANISO>::MINB;
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
     auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
