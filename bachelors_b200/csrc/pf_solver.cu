@@ -61,7 +61,7 @@ struct pf_solver {
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
     unsigned halo_attr_done = 0;            // same for k_stream_step_halo
     bool halo_in_kernel = false;            // the last fused launch did the halo hand-over itself
-    int stream_resident[16];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
+    int stream_resident[20];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
     unsigned* run_progress = nullptr;       // multi-step launches: steps finished by each unit (+ 1 flag word), see StreamRun
     int run_progress_units = 0;
     unsigned run_base = 0;                  // progress value meaning "nothing of the next launch done yet"
@@ -519,10 +519,10 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
     return best_n;
 }
 
-template <typename Real, int SCHEME, bool ANISO>
+template <typename Real, int SCHEME, bool ANISO, int MINB = StreamOcc<Real, SCHEME, ANISO>::MINB>
 static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
 {
-    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS, MINB = StreamOcc<Real, SCHEME, ANISO>::MINB;
+    constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS;
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
     auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
@@ -649,7 +649,23 @@ static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Re
     {
         case 0: return launch_euler_inst<Real, false>(s, a, base);
         case 1: return launch_euler_inst<Real, true>(s, a, base);
-        case 2: return launch_stream_inst<Real, SCHEME_RK4, false>(s, a, base);
+        case 2:
+            // explicit-rk4 without anisotropy, fp64 (the benchmark family): compiled for 5 CTAs per SM as well (96 registers, 16 bytes
+            // of spills) - taken when the grid is ONE wave at 5 per SM (2048^2: 72.6 against 75.1 us; 6 per SM: 76.0, 3: 85.8);
+            // the many-wave 16384 x 2048 slab stays at 4 (0.472 against 0.476 ms), and so do grids whose chunks would get shorter than 40
+            // rows at 5 per SM (1024^2: 28.0 us at 4, 30.9 at 5; 512^2: 24.5 / 30.1 - the pipeline fill of 9 rows per chunk)
+            if constexpr (sizeof(Real) == 8)
+            {
+                constexpr int NST = SchemeStages<SCHEME_RK4>::value, EWI = 32 * STREAM_WARPS - 2 * NST;
+                const int rows = a.own_y1 - a.own_y0;
+                if(rows > 0)
+                {
+                    const int strips = stream_strips(a.nx, EWI, NST, a.bc == PF_BOUNDARY_PERIODIC);
+                    const int nch = stream_chunks(s->sm_count, 5, strips, rows, StreamGeom<SCHEME_RK4>::FILL);
+                    if((long long) strips * nch <= (long long) s->sm_count * 5 && rows / nch >= 40) return launch_stream_inst<Real, SCHEME_RK4, false, 5>(s, a, 16);
+                }
+            }
+            return launch_stream_inst<Real, SCHEME_RK4, false>(s, a, base);
         case 3: return launch_stream_inst<Real, SCHEME_RK4, true>(s, a, base);
         case 4: return launch_stream_inst<Real, SCHEME_RKM, false>(s, a, base);
         default: return launch_stream_inst<Real, SCHEME_RKM, true>(s, a, base);
