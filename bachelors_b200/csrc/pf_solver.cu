@@ -57,11 +57,10 @@ struct pf_solver {
     double adaptive_tau = 0;                // simulation.cu:363
     int last_num_steps = 0;                 // simulation.cu:936
 
-    unsigned smem_attr_done = 0;            // bit per fused-kernel instance
     unsigned stream_attr_done = 0;          // bit per streaming-kernel instance
     unsigned halo_attr_done = 0;            // same for k_stream_step_halo
     bool halo_in_kernel = false;            // the last fused launch did the halo hand-over itself
-    int stream_resident[20];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
+    int stream_resident[32];                // co-resident CTAs per SM of each streaming-kernel instance (0 = not queried yet)
     unsigned* run_progress = nullptr;       // multi-step launches: steps finished by each unit (+ 1 flag word), see StreamRun
     int run_progress_units = 0;
     unsigned run_base = 0;                  // progress value meaning "nothing of the next launch done yet"
@@ -441,52 +440,6 @@ int pf_halo_region(const pf_solver* s, void* field, int side, void** send_ptr, v
 // -------------------------------------------------------------------------------------------------------
 // Fused explicit step launchers
 // -------------------------------------------------------------------------------------------------------
-template <int SCHEME> struct FusedGeom;                       // extended tile 64 x (TY*R), 512 threads
-template <> struct FusedGeom<SCHEME_EULER> { static constexpr int EW = 64, TY = 8, R = 5; };
-template <> struct FusedGeom<SCHEME_RK4>   { static constexpr int EW = 64, TY = 8, R = 5; };
-template <> struct FusedGeom<SCHEME_RKM>   { static constexpr int EW = 64, TY = 8, R = 4; };
-
-template <typename Real, int SCHEME, bool ANISO>
-static int launch_fused_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bit)
-{
-    using G = FusedGeom<SCHEME>;
-    constexpr int NST = SchemeStages<SCHEME>::value;
-    constexpr int EH = G::TY * G::R;
-    constexpr int TW = G::EW - 2 * NST, TH = EH - 2 * NST;
-    static_assert(TW > 0 && TH > 0, "tile too small for the stage count");
-    using V2 = typename Vec2T<Real>::type;
-    const size_t smem = sizeof(V2) * ((size_t) G::EW * EH + 2) * 2;      // two tiles, one pad element at each end of both
-    auto kern = k_fused_step<Real, SCHEME, ANISO, G::EW, G::TY, G::R>;
-    if(!(s->smem_attr_done & (1u << inst_bit)))
-    {
-        PF_CUDA(s, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        s->smem_attr_done |= 1u << inst_bit;
-    }
-    const int own_rows = a.own_y1 - a.own_y0;
-    if(own_rows <= 0) return PF_OK;
-    cudaStream_t stream = s->launch_stream ? s->launch_stream : s->stream;
-    dim3 grid((unsigned)((a.nx + TW - 1) / TW), (unsigned)((own_rows + TH - 1) / TH));
-    dim3 block(G::EW, G::TY);
-    kern<<<grid, block, smem, stream>>>(a);
-    PF_LAUNCH_CHECK(s);
-    return PF_OK;
-}
-
-template <typename Real>
-static int launch_tiled(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
-{
-    const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
-    switch(scheme * 2 + (aniso ? 1 : 0))
-    {
-        case 0: return launch_fused_inst<Real, SCHEME_EULER, false>(s, a, base);
-        case 1: return launch_fused_inst<Real, SCHEME_EULER, true>(s, a, base);
-        case 2: return launch_fused_inst<Real, SCHEME_RK4, false>(s, a, base);
-        case 3: return launch_fused_inst<Real, SCHEME_RK4, true>(s, a, base);
-        case 4: return launch_fused_inst<Real, SCHEME_RKM, false>(s, a, base);
-        default: return launch_fused_inst<Real, SCHEME_RKM, true>(s, a, base);
-    }
-}
-
 // ---- streaming kernel (pf_stream.cuh): launch geometry -------------------------------------------------
 // CTA = 4 warps (128 columns, 128 - 2*NST of them interior). Resident CTAs per SM by register budget:
 // Euler 8 (<= 64 registers), the multi-stage schemes 4 (<= 128 registers).
@@ -519,14 +472,15 @@ static int stream_chunks(int sm_count, int minb, int strips, int rows, int fill)
     return best_n;
 }
 
-template <typename Real, int SCHEME, bool ANISO, int MINB = StreamOcc<Real, SCHEME, ANISO>::MINB>
+// ANISO: bit 0 = anisotropy, bit 1 = the corrector-guess form of the right-hand side (simulation.cu:221-225; single-step launches only)
+template <typename Real, int SCHEME, int ANISO, int MINB = StreamOcc<Real, SCHEME, (ANISO & 1) != 0>::MINB>
 static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
 {
     constexpr int NST = SchemeStages<SCHEME>::value, W = STREAM_WARPS;
     constexpr int EWI = 32 * W - 2 * NST;
     static_assert(EWI > 0, "strip too narrow for the stage count");
     auto kern = k_stream_step<Real, SCHEME, ANISO, W, MINB>;
-    constexpr bool HAS_RUN = SCHEME == SCHEME_RK4;                          // the only scheme with a multi-step kernel (see below)
+    constexpr bool HAS_RUN = SCHEME == SCHEME_RK4 && ANISO < 2;             // the only scheme with a multi-step kernel (see below)
     const size_t smem = stream_smem_bytes<Real, SCHEME, W>();
     if(!(s->stream_attr_done & (1u << inst_bit)))
     {
@@ -587,7 +541,7 @@ static int launch_stream_inst(pf_solver* s, FusedArgs<Real> a, int inst_bit)
             return PF_OK;
         }
     }
-    if constexpr (SCHEME != SCHEME_EULER)
+    if constexpr (SCHEME != SCHEME_EULER && ANISO < 2)
     {
         // a linked slab (pf_halo_link), whole-slab launch: the halo hand-over happens inside the kernel
         if(a.halo_flags && s->halo_in_kernel_ok && own_rows / a.nch >= a.halo_g)
@@ -638,12 +592,22 @@ static int launch_euler_inst(pf_solver* s, const FusedArgs<Real>& a, int inst_bi
 }
 
 // One launch = one whole time step (or one Merson attempt): the Euler tile kernel (pf_euler.cuh) for the one-stage scheme, the
-// streaming kernel (pf_stream.cuh) for RK4 and Merson; a step with the corrector guess (a different right-hand side,
-// simulation.cu:221-225) takes the 2-D tiled kernel of pf_fused.cuh.
+// streaming kernel (pf_stream.cuh) for RK4 and Merson, with instantiations of their own for the corrector-guess form of the
+// right-hand side (simulation.cu:221-225). (Euler with the guess: the GENERAL tile kernel, euler_step_based.)
 template <typename Real>
 static int launch_fused(pf_solver* s, int scheme, bool aniso, const FusedArgs<Real>& a)
 {
-    if(a.k.do_corrector_guess) return launch_tiled<Real>(s, scheme, aniso, a);
+    if(a.k.do_corrector_guess && scheme != SCHEME_EULER)
+    {
+        const int bit = 17 + (sizeof(Real) == 8 ? 0 : 4) + (scheme == SCHEME_RKM ? 2 : 0) + (aniso ? 1 : 0);
+        switch((scheme == SCHEME_RKM ? 2 : 0) + (aniso ? 1 : 0))
+        {
+            case 0: return launch_stream_inst<Real, SCHEME_RK4, 2>(s, a, bit);
+            case 1: return launch_stream_inst<Real, SCHEME_RK4, 3>(s, a, bit);
+            case 2: return launch_stream_inst<Real, SCHEME_RKM, 2>(s, a, bit);
+            default: return launch_stream_inst<Real, SCHEME_RKM, 3>(s, a, bit);
+        }
+    }
     const int base = (sizeof(Real) == 8 ? 0 : 6) + scheme * 2 + (aniso ? 1 : 0);
     switch(scheme * 2 + (aniso ? 1 : 0))
     {
@@ -909,7 +873,7 @@ template <typename Real>
 static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
 {
     const Real tau = (Real) tau_d;
-    // (the tiled kernel that serves do_corrector_guess keeps the words on the device)
+    // (the corrector-guess instantiations keep the words on the device)
     const bool handover = s->rkm_handover && s->rkm_fused && !s->rkm_keep_errors && !p.do_corrector_guess && s->is_full_grid() && s->win_y1 <= s->win_y0;
     if(handover ? s->d_err_dirty : !s->rkm_keep_errors) PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 3 * sizeof(unsigned long long), s->stream));
     s->d_err_dirty = !handover;

@@ -117,7 +117,7 @@ __device__ __forceinline__ void stream_store_ghost(const FusedArgs<Real>& a, con
 // iteration and apply the y-boundary ghosts; otherwise the caller guarantees both are unnecessary.
 // `old` is the state as it was when the iteration began: everything a stage consumes comes from there, except its
 // N neighbour, which is what stage S-1 has just written to `st`.
-template <typename Real, int SCHEME, bool ANISO, int EW, bool CHECKED, int PH, int S>
+template <typename Real, int SCHEME, int ANISO, int EW, bool CHECKED, int PH, int S>
 __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const StreamCtx<Real>& c,
                                              const StreamState<Real, SCHEME>& old, StreamState<Real, SCHEME>& st, const int it)
 {
@@ -162,7 +162,8 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
         if(row == 0)               { SF = ghost_of(CF, a.bc); ST = ghost_of(CT, a.bc_T); }
     }
     Real kF, kT;
-    rhs_cell_lean<Real, ANISO>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);       // kT without the reference's "+ fu"
+    // ANISO: bit 0 = anisotropy, bit 1 = the corrector-guess form of the right-hand side (simulation.cu:221-225)
+    rhs_cell_lean<Real, (ANISO & 1) != 0, (ANISO & 2) != 0>(a.k, CF, e.x, w.x, NF, SF, CT, e.y, w.y, NT, ST, kF, kT);   // kT without the reference's "+ fu"
 
     Real nF = 0, nT = 0;
     if(SCHEME == SCHEME_EULER)
@@ -239,7 +240,7 @@ __device__ __forceinline__ void stream_stage(const FusedArgs<Real>& a, const Str
     }
 }
 
-template <typename Real, int SCHEME, bool ANISO, int EW, bool CHECKED, int PH, int S>
+template <typename Real, int SCHEME, int ANISO, int EW, bool CHECKED, int PH, int S>
 struct StreamStages {
     static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c,
                                                const StreamState<Real, SCHEME>& old, StreamState<Real, SCHEME>& st, const int it)
@@ -261,7 +262,7 @@ __device__ __forceinline__ unsigned stream_mem_row(const FusedArgs<Real>& a, int
 }
 
 // One row of the march. PH = it mod U.
-template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
+template <typename Real, int SCHEME, int ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
 __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                  const int it, const int rlo, const int rhi)
 {
@@ -308,7 +309,7 @@ __device__ __forceinline__ void stream_iteration(const FusedArgs<Real>& a, const
     __syncthreads();
 }
 
-template <typename Real, int SCHEME, bool ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
+template <typename Real, int SCHEME, int ANISO, int EW, bool EDGE, bool COHERENT, bool CHECKED, int PH>
 struct StreamIters {
     static __device__ __forceinline__ void run(const FusedArgs<Real>& a, const StreamCtx<Real>& c, StreamState<Real, SCHEME>& st,
                                                const int it0, const int rlo, const int rhi)
@@ -355,7 +356,7 @@ __device__ __forceinline__ int stream_tile_to_unit(const FusedArgs<Real>& a, con
 }
 
 // One time step of one unit: y(n) = (F, U) -> y(n+1) = (out_F, out_U).
-template <typename Real, int SCHEME, bool ANISO, int WARPS, bool COHERENT>
+template <typename Real, int SCHEME, int ANISO, int WARPS, bool COHERENT>
 __device__ __forceinline__ void stream_unit(const FusedArgs<Real>& a, const Real* in_F, const Real* in_U, Real* out_F, Real* out_U,
                                             typename Vec2T<Real>::type* const smem, const int strip, const int chunk)
 {
@@ -530,7 +531,7 @@ __device__ __noinline__ void stream_run_done(unsigned* mine, const unsigned valu
 }
 
 // One time step per launch.
-template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+template <typename Real, int SCHEME, int ANISO, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB)
 k_stream_step(const FusedArgs<Real> a)
 {
@@ -586,7 +587,7 @@ __device__ __noinline__ void stream_halo_forward(const Real* out_F, const Real* 
     }
 }
 
-template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+template <typename Real, int SCHEME, int ANISO, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB)
 k_stream_step_halo(const FusedArgs<Real> a)
 {
@@ -618,7 +619,7 @@ k_stream_step_halo(const FusedArgs<Real> a)
 }
 
 // r.n_steps time steps per launch (cooperative launch: all units co-resident).
-template <typename Real, int SCHEME, bool ANISO, int WARPS, int MINB>
+template <typename Real, int SCHEME, int ANISO, int WARPS, int MINB>
 __global__ void __launch_bounds__(32 * WARPS, MINB)
 k_stream_run(const FusedArgs<Real> a, const StreamRun r)
 {

@@ -17,6 +17,7 @@
 
 #include "../bachelors_b200/csrc/pf_common.cuh"
 #include "../bachelors_b200/csrc/pf_fused.cuh"
+#include "kbench_tiled.cuh"
 #include "../bachelors_b200/csrc/pf_stream.cuh"
 #include "../bachelors_b200/csrc/pf_euler.cuh"
 
