@@ -873,8 +873,7 @@ template <typename Real>
 static int rkm_attempt(pf_solver* s, const pf_params& p, double tau_d, const Real* F, const Real* U, Real* nF, Real* nU)
 {
     const Real tau = (Real) tau_d;
-    // (the corrector-guess instantiations keep the words on the device)
-    const bool handover = s->rkm_handover && s->rkm_fused && !s->rkm_keep_errors && !p.do_corrector_guess && s->is_full_grid() && s->win_y1 <= s->win_y0;
+    const bool handover = s->rkm_handover && s->rkm_fused && !s->rkm_keep_errors && s->is_full_grid() && s->win_y1 <= s->win_y0;
     if(handover ? s->d_err_dirty : !s->rkm_keep_errors) PF_CUDA(s, cudaMemsetAsync(s->d_err, 0, 3 * sizeof(unsigned long long), s->stream));
     s->d_err_dirty = !handover;
     if(s->rkm_fused)
