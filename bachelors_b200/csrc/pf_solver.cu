@@ -705,11 +705,9 @@ static int halo_push_both(pf_solver* s, void* nF, void* nU)
 
 static bool fused_eligible(const pf_solver* s, const pf_params& p)
 {
-    // the single-kernel paths share one load geometry for both fields: Phi and T both periodic or both not (any Dirichlet / Neumann mix);
-    // the tiled kernel that serves the corrector guess knows one boundary type only
+    // the single-kernel paths share one load geometry for both fields: Phi and T both periodic or both not (any Dirichlet / Neumann mix)
     const bool perF = p.Phi_boundary == PF_BOUNDARY_PERIODIC, perT = p.T_boundary == PF_BOUNDARY_PERIODIC;
     if(perF != perT) return false;
-    if(p.Phi_boundary != p.T_boundary && p.do_corrector_guess) return false;
     if(p.do_exact) return false;                                      // nonzero source term fu in every stage: general per-stage path
     if(perF && (s->slab.has_lo != s->slab.has_hi)) return false;
     return true;

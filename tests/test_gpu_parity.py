@@ -430,14 +430,16 @@ def test_streaming_kernel_takes_different_boundary_types_for_phi_and_t(solver, b
 
 @pytest.mark.parametrize("dtype", [PF_F64, PF_F32], ids=["f64", "f32"])
 @pytest.mark.parametrize("solver", ["explicit-rk4", "explicit-rk4-adaptive"])
-@pytest.mark.parametrize("bc,S_aniso,kind", [("periodic", 0.0, "noise"), ("neumann", 0.25, "interface"), ("dirichlet", 0.0, "interface")])
+@pytest.mark.parametrize("bc,S_aniso,kind", [("periodic", 0.0, "noise"), ("neumann", 0.25, "interface"), ("dirichlet", 0.0, "interface"),
+                                             (("dirichlet", "neumann"), 0.2, "noise")])
 def test_streaming_kernel_takes_the_corrector_guess_rhs(solver, bc, S_aniso, kind, dtype):
     """The corrector-guess form of the right-hand side (simulation.cu:221-225) runs on instantiations of the one-launch streaming
     kernel (round 1: a separate 2-D tiled kernel): one launch per step / attempt, bit-identical to the CPU oracle, with noisy
     fields (signed zeros included), anisotropy on and off, every boundary type, grids of several strips."""
     nx, ny, steps = 261, 150, 3
     tol = 1e-7 if dtype == PF_F64 else 1e-4
-    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=S_aniso, Phi_boundary=bc, T_boundary=bc, do_corrector_guess=1,
+    bcF, bcT = bc if isinstance(bc, tuple) else (bc, bc)
+    p = default_params(solver=solver, nx=nx, ny=ny, L0=nx / 128.0, S=S_aniso, Phi_boundary=bcF, T_boundary=bcT, do_corrector_guess=1,
                        Phi_tolerance=tol, T_tolerance=tol)
     npdt = np.float64 if dtype == PF_F64 else np.float32
     F0, U0 = seeded_fields(nx, ny, npdt, kind=kind)
