@@ -8,7 +8,7 @@ PF_OK, PF_ERR_INVALID, PF_ERR_NO_DEVICE, PF_ERR_CUDA, PF_ERR_OOM, PF_ERR_UNSUPPO
 PF_F32, PF_F64 = 0, 1
 
 # pf_option
-PF_OPT_HOST_BANDS, PF_OPT_SI_PER_KERNEL, PF_OPT_SI_GRID_SYNC, PF_OPT_HALO_IN_KERNEL, PF_OPT_RUN_GRAPHS = 0, 1, 2, 3, 4
+PF_OPT_HOST_BANDS, PF_OPT_SI_PER_KERNEL, PF_OPT_SI_GRID_SYNC, PF_OPT_HALO_IN_KERNEL, PF_OPT_RUN_GRAPHS, PF_OPT_SI_BLOCKS_PER_SM = 0, 1, 2, 3, 4, 5
 
 # Sim_Boundary_Type, reference simulation.h:27-32
 BOUNDARY_PERIODIC, BOUNDARY_DIRICHLET_ZERO, BOUNDARY_NEUMANN_ZERO = 0, 1, 2

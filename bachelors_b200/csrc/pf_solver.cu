@@ -68,6 +68,7 @@ struct pf_solver {
     cudaGraphExec_t run_graph = nullptr;
     struct RunGraphKey { const void *F, *U, *nF, *nU; pf_params p; } run_graph_key = {};
     bool run_graphs_ok = true;              // PF_OPT_RUN_GRAPHS; cleared when a capture fails
+    int si_blocks_per_sm = 4;               // PF_OPT_SI_BLOCKS_PER_SM: blocks of the CG kernels per SM (1 .. 4)
     int run_steps = 1;                      // steps the next fused launch advances (set by pf_run around its launch)
     bool run_used = false;                  // the last fused launch really was a multi-step launch
     int coop_blocks_per_sm[4] = {-1, -1, -1, -1};   // co-resident CTAs per SM of k_si_step_coop<Real, ANISO> (-1: not queried yet)
@@ -290,6 +291,7 @@ int pf_set_option(pf_solver* s, int option, int value)
         case PF_OPT_SI_PER_KERNEL: s->force_per_kernel_cg = value != 0; return PF_OK;
         case PF_OPT_SI_GRID_SYNC:  s->plain_grid_sync = value != 0; return PF_OK;
         case PF_OPT_RUN_GRAPHS:    s->run_graphs_ok = value != 0; return PF_OK;
+        case PF_OPT_SI_BLOCKS_PER_SM: if(value < 1 || value > 4) return fail(s, PF_ERR_INVALID, "PF_OPT_SI_BLOCKS_PER_SM: %d", value); s->si_blocks_per_sm = value; return PF_OK;
         case PF_OPT_HALO_IN_KERNEL: s->halo_in_kernel_ok = value != 0; return PF_OK;
         default: return fail(s, PF_ERR_INVALID, "pf_set_option: unknown option %d", option);
     }
@@ -1018,7 +1020,7 @@ static inline int cg_blocks(const pf_solver* s, int nx, int ny)
 {
     int segs = (nx + CG_THREADS - 1) / CG_THREADS;
     long long items = (long long) segs * ny;
-    long long want = std::min<long long>(items, (long long) s->sm_count * 4);
+    long long want = std::min<long long>(items, (long long) s->sm_count * s->si_blocks_per_sm);
     return (int) std::max<long long>(1, std::min<long long>(want, CG_MAX_BLOCKS));
 }
 

@@ -152,6 +152,7 @@ typedef enum pf_option {
     PF_OPT_SI_GRID_SYNC  = 2,  /* != 0: cooperative step with grid.sync() + partial arrays instead of the flagged all-block sums */
     PF_OPT_HALO_IN_KERNEL = 3, /* linked slabs (pf_halo_link), explicit-rk4: 1 = hand-over inside the step kernel, 0 = wait / push launches around it */
     PF_OPT_RUN_GRAPHS    = 4,  /* pf_run: batches of single-launch fixed-dt steps replayed as CUDA graphs of 64 steps (default 1) */
+    PF_OPT_SI_BLOCKS_PER_SM = 5, /* semi-implicit: blocks of the CG kernels per SM, 1 .. 4 (default 4) */
 } pf_option;
 PF_API int  pf_set_option(pf_solver* s, int option, int value);
 
